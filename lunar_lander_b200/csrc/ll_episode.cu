@@ -1,0 +1,448 @@
+// ll_episode.cu — K1: the fused episode kernel.  One persistent launch per generation evaluates every
+// (member, layout) episode of this GPU's shard: MLP forward -> argmax action -> lander update -> step penalty,
+// until touchdown or max_steps, then the terminal penalty and the per-member fitness.
+//
+// Replaces (reference file:line, azimonti/lunar-lander):
+//   NNEngineTrainer<T>::train_generation / sim_task          src/nn_engine_trainer.cpp:443-539
+//   GameLogicCpp<T>::reset/apply_action/update_physics/check_landing_crash/get_state/update
+//                                                              src/game_logic.cpp:124-310
+//   calculate_step_penalty / calculate_terminal_penalty(3-arg) src/game_logic.cpp:312-320, 352-388
+//   nn::ANN_MLP_GA<T>::feedforward (ma-libs, call site)        src/nn_engine_trainer.cpp:501-502
+//
+// Mapping.  A warp owns a tile of 32/G members, G = lanes per member (32 when n_layouts >= 32, else the next
+// power of two >= n_layouts).  Lane = one episode slot: its lander state, step counter and penalty accumulator
+// live in registers for the whole episode.  The tile's member rows are staged ONCE into shared memory by TMA
+// bulk copies (cp.async.bulk + mbarrier) in the k-major device layout, so that inside the dot products all lanes
+// of a member read the same 16-byte weight vector (a shared-memory broadcast) and each lane reads only its own
+// activation column [k][lane] (bank = lane, conflict free).  Lanes whose episode ended pull the member's next
+// layout from a shared-memory counter; warps pull tiles from a global counter (episodes last 9..max_steps steps).
+// Per-layout results are kept in shared memory and summed in layout order by one lane per member, in double,
+// exactly like the reference's accumulators (src/nn_engine_trainer.cpp:477-530).
+#include <stdio.h>
+
+#include "ll_ops.cuh"
+
+namespace
+{
+    struct ep_dev_args
+    {
+        const void* params;
+        const void* layouts;
+        int n_layouts, max_steps;
+        unsigned long long n_members;
+        double *fitness, *lr, *steps;
+        int* ep_steps;
+        double* ep_fit;
+        unsigned int* queue;
+        ll_step_rec* trace;
+        int trace_cap;
+        ll_episode_result* trace_result;
+        // geometry
+        int G, nslots;            // lanes per member, members per warp tile
+        unsigned int n_tiles;
+        int slot_stride;          // elements between member rows in shared memory
+        int off_w, off_act, off_fit, off_meta, warp_bytes; // byte offsets inside a warp's shared-memory slice
+    };
+
+    template <typename T, int N> struct vec_loader;
+    template <int N> struct vec_loader<float, N>
+    {
+        static __device__ __forceinline__ void load(const float* p, float* v)
+        {
+#pragma unroll
+            for (int i = 0; i < N; i += 4)
+            {
+                const float4 q = *reinterpret_cast<const float4*>(p + i);
+                v[i] = q.x, v[i + 1] = q.y, v[i + 2] = q.z, v[i + 3] = q.w;
+            }
+        }
+    };
+    template <int N> struct vec_loader<double, N>
+    {
+        static __device__ __forceinline__ void load(const double* p, double* v)
+        {
+#pragma unroll
+            for (int i = 0; i < N; i += 2)
+            {
+                const double2 q = *reinterpret_cast<const double2*>(p + i);
+                v[i] = q.x, v[i + 1] = q.y;
+            }
+        }
+    };
+
+    // TILE consecutive output neurons of one layer for this lane's episode.
+    //   w   : &Wt[0][o0] of the lane's member (shared memory), row pitch out_pad
+    //   ain : this lane's activation column of the previous layer, element k at ain[k * 32]
+    template <typename T, int MODE, int TILE>
+    __device__ __forceinline__ void layer_tile(const T* __restrict__ w, const T* __restrict__ b, const T* __restrict__ ain,
+                                               T* __restrict__ aout, int in, int out_pad, int act)
+    {
+        using O = ll_ops<T, MODE>;
+        T acc[TILE];
+#pragma unroll
+        for (int i = 0; i < TILE; ++i) acc[i] = T(0);
+#pragma unroll 2
+        for (int k = 0; k < in; ++k)
+        {
+            const T a = ain[k * 32];
+            T wv[TILE];
+            vec_loader<T, TILE>::load(w + k * out_pad, wv);
+#pragma unroll
+            for (int i = 0; i < TILE; ++i) acc[i] = O::madd(acc[i], wv[i], a);
+        }
+        T bv[TILE];
+        vec_loader<T, TILE>::load(b, bv);
+#pragma unroll
+        for (int i = 0; i < TILE; ++i) aout[i * 32] = O::act(O::add(acc[i], bv[i]), act);
+    }
+
+    // Whole forward pass; returns the index of the first maximum of the output layer.
+    template <typename T, int MODE>
+    __device__ __forceinline__ int forward(const ll_topo& tp, const T* __restrict__ wrow, T* a0, T* a1)
+    {
+        constexpr int BIG = sizeof(T) == 4 ? 16 : 8;
+        T* ain  = a0;
+        T* aout = a1;
+        for (int l = 0; l < tp.n_layers; ++l)
+        {
+            const int in = tp.in[l], op = tp.out_pad[l];
+            const T* w = wrow + tp.w_off[l];
+            const T* b = wrow + tp.b_off[l];
+            int o      = 0;
+            for (; o + BIG <= op; o += BIG) layer_tile<T, MODE, BIG>(w + o, b + o, ain, aout + o * 32, in, op, tp.activation);
+            if (BIG == 16 && o + 8 <= op)
+            {
+                layer_tile<T, MODE, 8>(w + o, b + o, ain, aout + o * 32, in, op, tp.activation);
+                o += 8;
+            }
+            if (o + 4 <= op)
+            {
+                layer_tile<T, MODE, 4>(w + o, b + o, ain, aout + o * 32, in, op, tp.activation);
+                o += 4;
+            }
+            T* t = ain;
+            ain  = aout;
+            aout = t;
+        }
+        const int n_out = tp.out[tp.n_layers - 1];
+        int best        = 0;
+        T vbest         = ain[0];
+        for (int j = 1; j < n_out; ++j)
+        {
+            const T v = ain[j * 32];
+            if (v > vbest) vbest = v, best = j;
+        }
+        return best;
+    }
+
+    template <typename T> __device__ __forceinline__ T clampT(T v, T lo, T hi) { return v < lo ? lo : (hi < v ? hi : v); }
+    __device__ __forceinline__ float absT(float v) { return fabsf(v); }
+    __device__ __forceinline__ double absT(double v) { return fabs(v); }
+
+    // get_state(): src/game_logic.cpp:275-293
+    template <typename T, int MODE>
+    __device__ __forceinline__ void write_state(const ll_env<T>& e, T x, T y, T vx, T vy, T fuel, T cx, T* col)
+    {
+        using O = ll_ops<T, MODE>;
+        T s0, s1, s2, s3, s4;
+        const T dx = O::sub(x, cx), dy = O::sub(y, e.pad_y);
+        if (O::fast)
+        {
+            s0 = O::mul(vx, e.inv_max_vx), s1 = O::mul(vy, e.inv_max_vy), s2 = O::mul(dx, e.inv_width);
+            s3 = O::mul(dy, e.inv_height), s4 = O::mul(fuel, e.inv_max_fuel);
+        }
+        else
+        {
+            s0 = O::div(vx, e.max_vx), s1 = O::div(vy, e.max_vy), s2 = O::div(dx, e.width);
+            s3 = O::div(dy, e.height), s4 = O::div(fuel, e.max_fuel);
+        }
+        col[0 * 32] = clampT(s0, T(-2), T(2));
+        col[1 * 32] = clampT(s1, T(-2), T(2));
+        col[2 * 32] = clampT(s2, T(-5), T(5));
+        col[3 * 32] = clampT(s3, T(-5), T(5));
+        col[4 * 32] = s4;
+    }
+
+    template <typename T, int MODE>
+    __global__ void __launch_bounds__(128) ll_episode_kernel(const __grid_constant__ ll_topo tp, const __grid_constant__ ll_env<T> env,
+                                                             const __grid_constant__ ep_dev_args a)
+    {
+        using O = ll_ops<T, MODE>;
+        extern __shared__ __align__(128) unsigned char smem_raw[];
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        unsigned char* ws = smem_raw + (size_t)warp * a.warp_bytes;
+        uint64_t* bar     = reinterpret_cast<uint64_t*>(ws);
+        int* next_layout  = reinterpret_cast<int*>(ws + 16);
+        T* wsm            = reinterpret_cast<T*>(ws + a.off_w);
+        T* act0           = reinterpret_cast<T*>(ws + a.off_act) + lane;
+        T* act1           = act0 + tp.max_width * 32;
+        double* res_fit   = reinterpret_cast<double*>(ws + a.off_fit);
+        int* res_meta     = reinterpret_cast<int*>(ws + a.off_meta);
+
+        const int G = a.G, L = a.n_layouts;
+        const int slot = lane / G, j = lane - slot * G;
+        const T* wrow  = wsm + (size_t)slot * a.slot_stride;
+        const ll_layout<T>* layouts = static_cast<const ll_layout<T>*>(a.layouts);
+        const uint32_t row_bytes    = (uint32_t)tp.p_dev * sizeof(T);
+
+        if (lane == 0) ll_mbar_init(bar, 1);
+        __syncwarp();
+        uint32_t phase = 0;
+
+        for (;;)
+        {
+            unsigned int tile = 0;
+            if (lane == 0) tile = atomicAdd(a.queue, 1u);
+            tile = __shfl_sync(0xffffffffu, tile, 0);
+            if (tile >= a.n_tiles) break;
+            const unsigned long long m0 = (unsigned long long)tile * a.nslots;
+            const int nvalid            = (int)min((unsigned long long)a.nslots, a.n_members - m0);
+            const unsigned long long member = m0 + slot;
+            const bool valid                = slot < nvalid;
+
+            // ---- stage the tile's member rows: TMA bulk copies, completion on the warp's mbarrier
+            if (lane == 0) ll_mbar_expect_tx(bar, row_bytes * (uint32_t)nvalid);
+            __syncwarp();
+            if (lane < nvalid)
+                ll_bulk_g2s(wsm + (size_t)lane * a.slot_stride, static_cast<const T*>(a.params) + (m0 + lane) * (size_t)tp.p_dev, row_bytes, bar);
+            if (j == 0) next_layout[slot] = min(G, L);
+            __syncwarp();
+            ll_mbar_wait(bar, phase);
+            phase ^= 1u;
+
+            // ---- per-lane episode state (registers)
+            T x = T(0), y = T(0), vx = T(0), vy = T(0), fuel = T(0), cx = T(0), lpad = T(0), lpad_r = T(0);
+            int dir = 0, layout = -1, steps = 0;
+            double acc  = 0.0;
+            bool active = false;
+            auto begin_episode = [&](int l) {
+                const ll_layout<T> lay = layouts[l];
+                layout = l, dir = lay.dir, cx = lay.center_x, lpad = lay.lpad_x1, lpad_r = lay.lpad_right;
+                x = lay.init_x, y = env.y0, vx = env.vx0, vy = env.vy0, fuel = env.max_fuel;
+                steps = 0, acc = 0.0;
+            };
+            if (valid && j < L)
+            {
+                begin_episode(j);
+                active = true;
+            }
+            const bool tracer = a.trace != nullptr && tile == 0 && lane == 0;
+
+            while (__any_sync(0xffffffffu, active))
+            {
+                write_state<T, MODE>(env, x, y, vx, vy, fuel, cx, act0);
+                const int action = forward<T, MODE>(tp, wrow, act0, act1);
+                if (active)
+                {
+                    // apply_action: src/game_logic.cpp:156-183
+                    if (fuel > T(0))
+                    {
+                        if (action == 1) vy = O::sub(vy, T(0.3)), fuel = O::sub(fuel, T(1.0));
+                        else if (action == 2) vx = O::sub(vx, T(0.05)), fuel = O::sub(fuel, T(0.5));
+                        else if (action == 3) vx = O::add(vx, T(0.05)), fuel = O::sub(fuel, T(0.5));
+                        fuel = (T(0) < fuel) ? fuel : T(0);
+                    }
+                    // update_physics: :185-195
+                    vy = O::add(vy, env.ay);
+                    vx = O::mul(vx, env.one_minus_mu_x);
+                    vy = O::mul(vy, env.one_minus_mu_y);
+                    x  = O::add(x, vx);
+                    y  = O::add(y, vy);
+                    // check_landing_crash: :197-239 (skipped on the very first step)
+                    bool landed = false, success = false;
+                    if (steps != 0 && y >= env.ground)
+                    {
+                        y      = env.ground;
+                        landed = true;
+                        const bool on_pad = (x >= lpad) && (O::add(x, env.lander_w) <= lpad_r);
+                        const bool safe   = (absT(vx) < env.max_vx) && (absT(vy) < env.max_vy);
+                        success           = on_pad && safe;
+                        vx = T(0), vy = T(0);
+                    }
+                    // calculate_step_penalty on the post-update state: :312-320, accumulated in double (trainer :507-508)
+                    const T dist = O::add(absT(O::sub(x, cx)), absT(O::sub(y, env.pad_y)));
+                    T sp         = O::add(T(0), O::mul(dist, env.sp_dist));
+                    if (action > 0) sp = O::add(sp, env.sp_action);
+                    acc = __dadd_rn(acc, (double)sp);
+                    if (tracer && steps < a.trace_cap)
+                    {
+                        ll_step_rec r;
+                        r.action = (double)action;
+                        write_state<T, MODE>(env, x, y, vx, vy, fuel, cx, act0);
+                        for (int i = 0; i < 5; ++i) r.state[i] = (double)act0[i * 32];
+                        r.x = (double)x, r.y = (double)y, r.vx = (double)vx, r.vy = (double)vy, r.fuel = (double)fuel;
+                        a.trace[steps] = r;
+                    }
+                    ++steps;
+                    if (landed || steps >= a.max_steps)
+                    {
+                        // calculate_terminal_penalty(steps, direction, bonus): :352-388
+                        const bool crashed = landed && !success;
+                        T term = O::add(T(0), O::mul((T)steps, env.tp_steps));
+                        term   = O::add(term, O::mul(dist, env.tp_dist));
+                        if (success)
+                        {
+                            term = O::sub(term, env.tp_landed_bonus);
+                            term = O::sub(term, O::mul(fuel, env.tp_fuel_bonus));
+                        }
+                        else if (crashed)
+                        {
+                            term = O::add(term, env.tp_crashed);
+                            term = O::add(term, O::mul(O::sqrt(O::add(O::mul(vx, vx), O::mul(vy, vy))), env.tp_crash_v_mag));
+                        }
+                        else if (fuel <= T(0) && !landed) { term = O::add(term, env.tp_no_fuel); }
+                        if (!success) term = O::add(term, O::mul(O::sqrt(O::add(O::mul(vx, vx), O::mul(vy, vy))), T(1.0)));
+                        const double fit = __dadd_rn((double)term, acc);
+                        const int meta   = steps | (landed ? (1 << 28) : 0) | (crashed ? (1 << 29) : 0) | (success ? (1 << 30) : 0);
+                        const int ridx   = slot * L + layout;
+                        res_fit[ridx]    = fit;
+                        res_meta[ridx]   = meta;
+                        if (a.ep_steps)
+                        {
+                            a.ep_steps[member * (size_t)L + layout] = meta;
+                            a.ep_fit[member * (size_t)L + layout]   = fit;
+                        }
+                        if (tracer && a.trace_result)
+                        {
+                            ll_episode_result r;
+                            r.steps = steps, r.flags = (landed ? 1 : 0) | (crashed ? 2 : 0) | (success ? 4 : 0);
+                            r.step_penalty_sum = acc, r.terminal_penalty = (double)term;
+                            r.bonus_lr[0] = r.bonus_lr[1] = 0.0;
+                            if (success) r.bonus_lr[dir] = (double)O::add(T(0), env.tp_landed_lr_bonus);
+                            *a.trace_result = r;
+                        }
+                        const int nl = atomicAdd(&next_layout[slot], 1);
+                        if (nl < L) begin_episode(nl);
+                        else active = false;
+                    }
+                }
+                __syncwarp();
+            }
+
+            // ---- per-member totals in layout order: src/nn_engine_trainer.cpp:518-530
+            __syncwarp();
+            if (valid && j == 0)
+            {
+                double total = 0.0, total_steps = 0.0;
+                T bonus0 = T(0), bonus1 = T(0);
+                for (int l = 0; l < L; ++l)
+                {
+                    const int meta = res_meta[slot * L + l];
+                    total          = __dadd_rn(total, res_fit[slot * L + l]);
+                    total_steps    = __dadd_rn(total_steps, (double)(meta & 0x0fffffff));
+                    if (meta & (1 << 30))
+                    {
+                        if (layouts[l].dir == 0) bonus0 = O::add(bonus0, env.tp_landed_lr_bonus);
+                        else bonus1 = O::add(bonus1, env.tp_landed_lr_bonus);
+                    }
+                }
+                const double lr = (double)((bonus1 < bonus0) ? bonus1 : bonus0);
+                a.fitness[member] = __dsub_rn(total, lr);
+                a.lr[member]      = lr;
+                a.steps[member]   = total_steps;
+            }
+            __syncwarp(); // all lanes are done with this tile's shared memory before it is overwritten
+        }
+    }
+
+    // Single forward pass on a given state (ll_feedforward_index): one warp, lane 0's answer.
+    template <typename T, int MODE>
+    __global__ void ll_feedforward_kernel(const __grid_constant__ ll_topo tp, const T* __restrict__ row, const T* __restrict__ state,
+                                          unsigned long long* action)
+    {
+        extern __shared__ __align__(128) unsigned char smem_raw[];
+        T* wsm  = reinterpret_cast<T*>(smem_raw);
+        T* act0 = wsm + tp.p_dev + threadIdx.x;
+        T* act1 = act0 + tp.max_width * 32;
+        for (int i = threadIdx.x; i < tp.p_dev; i += 32) wsm[i] = row[i];
+        __syncwarp();
+        for (int i = 0; i < tp.in[0]; ++i) act0[i * 32] = state[i];
+        const int best = forward<T, MODE>(tp, wsm, act0, act1);
+        if (threadIdx.x == 0) *action = (unsigned long long)best;
+    }
+
+    template <typename T, int MODE> int launch_t(ll_ctx* ctx, const ll_episode_args& h)
+    {
+        const ll_topo& tp = ctx->topo;
+        ep_dev_args a;
+        a.params = h.params, a.layouts = h.layouts, a.n_layouts = h.n_layouts, a.max_steps = h.max_steps;
+        a.n_members = h.n_members, a.fitness = h.fitness, a.lr = h.lr, a.steps = h.steps;
+        a.ep_steps = h.ep_steps, a.ep_fit = h.ep_fit, a.queue = h.queue;
+        a.trace = h.trace, a.trace_cap = h.trace_cap, a.trace_result = h.trace_result;
+        const int L = h.n_layouts;
+        int G       = 32;
+        if (L < 32)
+        {
+            G = 1;
+            while (G < L) G <<= 1;
+        }
+        a.G = G, a.nslots = 32 / G;
+        a.n_tiles = (unsigned int)((h.n_members + a.nslots - 1) / a.nslots);
+        // member rows in shared memory: pitch == 4 words (mod 32) so that 16-byte reads of the same element by
+        // lanes of different members fall into different bank groups
+        int stride_words = tp.p_dev * (int)(sizeof(T) / 4);
+        while (a.nslots > 1 && (stride_words % 32) != 4) stride_words += 4;
+        a.slot_stride = stride_words / (int)(sizeof(T) / 4);
+        auto up       = [](int v) { return (v + 127) & ~127; };
+        a.off_w       = 256;
+        a.off_act     = up(a.off_w + a.nslots * a.slot_stride * (int)sizeof(T));
+        a.off_fit     = up(a.off_act + 2 * tp.max_width * 32 * (int)sizeof(T));
+        const int R   = L > 32 ? L : 32;
+        a.off_meta    = a.off_fit + R * 8;
+        a.warp_bytes  = up(a.off_meta + R * 4);
+
+        int max_smem = 0;
+        LL_CUDA(ctx, cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device));
+        if (a.warp_bytes > max_smem)
+            return ll_fail(ctx, LL_EINVAL, "topology needs " + std::to_string(a.warp_bytes) + " B of shared memory per warp, device allows " + std::to_string(max_smem));
+        int wpb = 4;
+        while (wpb > 1 && wpb * a.warp_bytes > max_smem / 2) wpb >>= 1; // prefer >= 2 blocks per SM
+        const size_t smem = (size_t)wpb * a.warp_bytes;
+        auto kern         = ll_episode_kernel<T, MODE>;
+        LL_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int per_sm = 0;
+        LL_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, wpb * 32, smem));
+        if (per_sm < 1) return ll_fail(ctx, LL_EINVAL, "episode kernel does not fit on an SM");
+        unsigned int blocks_needed = (a.n_tiles + wpb - 1) / wpb;
+        unsigned int grid          = (unsigned int)(per_sm * ctx->sm_count);
+        if (grid > blocks_needed) grid = blocks_needed;
+        if (grid < 1) grid = 1;
+        ll_env<T> env;
+        ll_make_env<T>(ctx->env_cfg, MODE == LL_MODE_FAST, &env);
+        LL_CUDA(ctx, cudaMemsetAsync(h.queue, 0, sizeof(unsigned int), ctx->stream));
+        kern<<<grid, wpb * 32, smem, ctx->stream>>>(tp, env, a);
+        LL_CUDA(ctx, cudaGetLastError());
+        return LL_OK;
+    }
+
+    template <typename T, int MODE> int launch_ff(ll_ctx* ctx, const void* row, const void* state, unsigned long long* action)
+    {
+        const ll_topo& tp = ctx->topo;
+        const size_t smem = ((size_t)tp.p_dev + 2 * (size_t)tp.max_width * 32) * sizeof(T);
+        auto kern         = ll_feedforward_kernel<T, MODE>;
+        LL_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<1, 32, smem, ctx->stream>>>(tp, static_cast<const T*>(row), static_cast<const T*>(state), action);
+        LL_CUDA(ctx, cudaGetLastError());
+        return LL_OK;
+    }
+} // namespace
+
+int ll_launch_episode(ll_ctx* ctx, const ll_episode_args& a)
+{
+    if (ctx->precision == 64) return launch_t<double, LL_MODE_EXACT>(ctx, a);
+    if (ctx->mode == LL_MODE_FAST) return launch_t<float, LL_MODE_FAST>(ctx, a);
+    return launch_t<float, LL_MODE_EXACT>(ctx, a);
+}
+
+int ll_launch_feedforward(ll_ctx* ctx, const void* member_row, const void* d_state, unsigned long long* d_action)
+{
+    if (ctx->precision == 64) return launch_ff<double, LL_MODE_EXACT>(ctx, member_row, d_state, d_action);
+    if (ctx->mode == LL_MODE_FAST) return launch_ff<float, LL_MODE_FAST>(ctx, member_row, d_state, d_action);
+    return launch_ff<float, LL_MODE_EXACT>(ctx, member_row, d_state, d_action);
+}
+
+const char* ll_episode_kernel_name(const ll_ctx* ctx, int)
+{
+    if (ctx->precision == 64) return "ll_episode_kernel<double,exact>";
+    return ctx->mode == LL_MODE_FAST ? "ll_episode_kernel<float,fast>" : "ll_episode_kernel<float,exact>";
+}

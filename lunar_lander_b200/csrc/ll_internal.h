@@ -1,0 +1,167 @@
+// ll_internal.h — private types shared by the translation units of libll_gpu.so (not part of the ABI).
+#ifndef LL_INTERNAL_H_
+#define LL_INTERNAL_H_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/ll_gpu.h"
+
+#define LL_MAX_LAYERS 16 /* weight layers (n_sizes - 1) */
+#define LL_MAX_WIDTH 1024
+#define LL_MAX_LAYOUTS 4096
+#define LL_MAX_TOP 4096
+
+// Network topology in the device ("forward") layout.  A member row holds, for each layer l:
+//   Wt_l[k][out_pad_l]  k = 0..in_l-1   (k-major = transposed w.r.t. the weight file's [out][in]; pad columns are 0)
+//   b_l[out_pad_l]
+// out_pad_l = out_l rounded up to a multiple of 4, so every k-row starts on a 16-byte boundary for
+// both float (LDS.128 = 4 outputs) and double (LDS.128 = 2 outputs).
+struct ll_topo
+{
+    int n_layers;
+    int max_width; // max over layers of out_pad (and the input width)
+    int p_canon;   // P = sum(in*out + out)
+    int p_dev;     // elements per member row in HBM / shared memory (multiple of 4)
+    int in[LL_MAX_LAYERS], out[LL_MAX_LAYERS], out_pad[LL_MAX_LAYERS];
+    int w_off[LL_MAX_LAYERS], b_off[LL_MAX_LAYERS]; // element offsets inside a device row
+    int activation;                                  // LL_ACT_*
+};
+
+// Every constant GameLogicCpp<T> derives from the configuration (src/game_logic.cpp:48-122), already
+// converted to T on the host with the same static_cast<T>(double) the reference applies.
+template <typename T> struct ll_env
+{
+    T pad_y, ground, max_vx, max_vy, ay, one_minus_mu_x, one_minus_mu_y;
+    T lander_w, lpad_w, width, height, max_fuel;
+    T y0, vx0, vy0;
+    T sp_dist, sp_action;
+    T tp_steps, tp_dist, tp_landed_bonus, tp_landed_lr_bonus, tp_fuel_bonus, tp_crashed, tp_crash_v_mag, tp_no_fuel;
+    // fast mode only: reciprocals so that get_state() multiplies instead of dividing
+    T inv_max_vx, inv_max_vy, inv_width, inv_height, inv_max_fuel;
+};
+
+// Per-layout values reset(spad_x1, lpad_x1) derives (src/game_logic.cpp:143-154, :101-122), in T.
+template <typename T> struct ll_layout
+{
+    T init_x, lpad_x1, lpad_right, center_x;
+    int dir, pad_;
+};
+
+struct ll_select_state
+{
+    unsigned long long prefix_hi;
+    unsigned int prefix_lo;
+    unsigned int k_rem;
+    unsigned int ticket;
+    unsigned int n_cand;
+    unsigned int hist[256];
+};
+
+struct ll_stats_dev
+{
+    double best_fitness, sum_fitness, sum_steps, best_lr;
+    unsigned long long best_index;
+    double steps_accum;               // running total of lander steps over evaluations (ll_step_counter)
+    unsigned long long evals_accum;   // number of evaluations accumulated
+};
+
+struct ll_ctx
+{
+    // configuration
+    ll_env_cfg env_cfg;
+    std::vector<uint64_t> sizes;
+    ll_topo topo;
+    uint64_t pop_global = 0, pop_local = 0, first_global = 0, top = 0, seed = 0, epochs = 0;
+    int precision = 32, mode = LL_MODE_EXACT, rank = 0, world = 1, device = 0, sm_count = 0;
+    int strategy = LL_STRATEGY_MIXED_WITH_RANDOM_INJECTION;
+    double ratio = 0.0, sigma_init = 1.0, sigma_mut = 0.1;
+    bool has_elites = false, have_results = false;
+    size_t elt = 4; // sizeof(T)
+    char device_name[64] = {0};
+    char kernel_name[64] = {0};
+
+    // device memory
+    void* d_params   = nullptr; // [pop_local][p_dev] T
+    void* d_elites   = nullptr; // [top][p_dev] T
+    int* d_dev2canon = nullptr; // [p_dev]
+    void* d_layouts  = nullptr; // [n_layouts] ll_layout<T>
+    int n_layouts = 0, layouts_cap = 0;
+    double *d_fitness = nullptr, *d_lr = nullptr, *d_steps = nullptr; // [pop_local]
+    int* d_ep_steps = nullptr;                                        // [pop_local][n_layouts] steps | flags<<24.. (see kernel)
+    double* d_ep_fit = nullptr;                                       // [pop_local][n_layouts]
+    size_t ep_cap   = 0;
+    unsigned int* d_queue   = nullptr;
+    ll_stats_dev* d_stats   = nullptr;
+    double* d_partials      = nullptr; // stats partials
+    ll_select_state* d_sel  = nullptr;
+    unsigned long long* d_keys = nullptr; // [pop_local] orderable fitness keys
+    ll_cand* d_cand         = nullptr;    // [LL_MAX_TOP] sorted candidates
+    unsigned long long* d_elite_idx = nullptr; // [top] global indices of the current elites
+    ll_step_rec* d_trace    = nullptr;
+    int trace_cap = 0;
+    void* d_scratch = nullptr; // small scratch (feedforward state, episode result)
+
+    // pinned host staging
+    void* h_pin = nullptr;
+    size_t h_pin_bytes = 0;
+
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+
+    // profiling
+    bool profile = false;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    ll_kernel_times times = {};
+
+    std::string err;
+};
+
+// ---- error plumbing ------------------------------------------------------------------------------------------
+void ll_set_error(ll_ctx* ctx, const std::string& msg);
+int ll_fail(ll_ctx* ctx, int code, const std::string& msg);
+#define LL_CUDA(ctx, call)                                                                                           \
+    do {                                                                                                             \
+        cudaError_t e__ = (call);                                                                                    \
+        if (e__ != cudaSuccess)                                                                                      \
+            return ll_fail((ctx), LL_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e__));                    \
+    } while (0)
+
+// ---- kernel launchers (one per translation unit) ---------------------------------------------------------------
+// episode kernels (ll_episode.cu)
+struct ll_episode_args
+{
+    const void* params;     // [members][p_dev]
+    const void* layouts;    // ll_layout<T>[n_layouts]
+    int n_layouts;
+    int max_steps;
+    uint64_t n_members;     // members in `params`
+    double *fitness, *lr, *steps; // [n_members]
+    int* ep_steps;          // [n_members][n_layouts] or null
+    double* ep_fit;         // [n_members][n_layouts] or null
+    unsigned int* queue;    // work counter (zeroed by the launcher)
+    ll_step_rec* trace;     // non-null: record every step of (member 0 of params, layout 0)
+    int trace_cap;
+    ll_episode_result* trace_result;
+};
+int ll_launch_episode(ll_ctx* ctx, const ll_episode_args& a);
+int ll_launch_feedforward(ll_ctx* ctx, const void* member_row, const void* d_state, unsigned long long* d_action);
+const char* ll_episode_kernel_name(const ll_ctx* ctx, int n_layouts);
+
+// GA kernels (ll_ga.cu)
+// generation key `gen`: epochs for the initial population / a reload, epochs + 1 for the children of a generation
+int ll_launch_create_population_gen(ll_ctx* ctx, int elitism, uint64_t gen);
+size_t ll_stats_partial_bytes(unsigned long long pop_local);
+int ll_launch_stats(ll_ctx* ctx);
+int ll_launch_topk(ll_ctx* ctx, unsigned int k); // fills d_cand[0..k) sorted by (fitness, global index)
+int ll_launch_gather(ll_ctx* ctx, const unsigned long long* d_idx, unsigned int n, void* d_out, int zero_unowned);
+
+// host helpers (ll_host.cpp)
+template <typename T> void ll_make_env(const ll_env_cfg& c, int fast, ll_env<T>* out);
+template <typename T> void ll_make_layout(const ll_env_cfg& c, int spad_x1, int lpad_x1, int dir, ll_layout<T>* out);
+void ll_build_topo(const std::vector<uint64_t>& sizes, int activation, ll_topo* t, std::vector<int>* dev2canon);
+
+#endif

@@ -1,0 +1,365 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI (lunar_lander_b200.Engine -> libll_gpu.so),
+against the CPU oracle (oracle/) on the same seeded inputs, against the committed golden fixtures, and through
+size-independent properties at BASELINE.json's full sizes.
+
+Bars: LL_MODE_EXACT (fp64 and fp32) is BIT-EXACT on actions, step counts, flags, per-step state, fitness and elite
+indices.  LL_MODE_FAST (fp32, FMA + tanh.approx) is judged on outcome rates and mean fitness, tolerances in the test.
+"""
+import numpy as np
+import pytest
+
+import util
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ll(built):
+    import lunar_lander_b200 as m
+    return m
+
+
+@pytest.fixture(scope="module")
+def po(built):
+    import pyoracle
+    return pyoracle
+
+
+def _engine(ll, sizes, pop, precision=64, mode=0, top=None, **kw):
+    cfg = util.cfg_for(sizes, **kw.pop("cfg", {}))
+    return ll.Engine(cfg, population=pop, top=top or min(10, pop), precision=precision, mode=mode, **kw), cfg
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# 1. reference-owned known answers: constant-action policies through the whole kernel
+@pytest.mark.parametrize("precision", [64, 32])
+def test_constant_action_known_answers(ll, precision):
+    sizes = [5, 16, 16, 4]
+    eng, cfg = _engine(ll, sizes, 4, precision)
+    for a in range(4):
+        eng.set_members(a, util.constant_action_member(sizes, a)[None, :])
+    for g in util.golden()["env_known_answers"]:
+        if g["precision"] != precision:
+            continue
+        rec, res = eng.trace_episode(g["action"], g["spad_x1"], g["lpad_x1"], 0, g["max_steps"])
+        assert res.steps == g["steps"] and res.flags == g["flags"]
+        assert res.step_penalty_sum == g["step_penalty_sum"]
+        assert res.terminal_penalty == g["terminal_penalty"]
+        assert np.all(rec[:, 0] == g["action"])
+        assert rec[-1, 6:11].tolist() == g["final"]
+        assert rec[-1, 1:6].tolist() == g["final_state"]
+    eng.close()
+
+
+# 2. per-step traces of random and elite policies, bit-exact
+@pytest.mark.parametrize("precision", [64, 32])
+@pytest.mark.parametrize("topo", ["16_16", "8_16_32_16_8", "32_128_32"])
+def test_trace_bit_exact(ll, po, precision, topo):
+    sizes = util.TOPOLOGIES[topo]
+    e, _ = util.elites(topo)
+    members = np.concatenate([e[:2], util.random_population(sizes, 3, 7)])
+    eng, cfg = _engine(ll, sizes, len(members), precision)
+    eng.set_members(0, members)
+    dt = eng.dtype
+    spad, lpad, d = util.layouts(8)
+    for m in range(len(members)):
+        for l in (0, 5):
+            rec, res = eng.trace_episode(m, int(spad[l]), int(lpad[l]), int(d[l]), 3000)
+            want = po.trace(cfg.env_cfg(), sizes, 1, members[m].astype(dt), spad[l], lpad[l], int(d[l]), 3000, precision)
+            assert res.steps == want["steps"] and res.flags == want["flags"]
+            assert np.array_equal(rec, want["rec"])
+            assert res.step_penalty_sum == want["acc"] and res.terminal_penalty == want["term"]
+            assert (res.bonus_lr[0], res.bonus_lr[1]) == want["bonus"]
+    eng.close()
+
+
+# 3. whole generations: fitness / lr / steps vectors and per-episode outcomes, every lane-group geometry
+@pytest.mark.parametrize("precision", [64, 32])
+@pytest.mark.parametrize("n_layouts", [1, 3, 8, 33, 50])
+def test_generation_bit_exact(ll, po, precision, n_layouts):
+    topo = "8_16_8"
+    pe, sizes = util.elite_population(topo, 40, 3)
+    members = np.concatenate([pe, util.random_population(sizes, 57, 11)])  # 97: ragged last tile
+    eng, cfg = _engine(ll, sizes, len(members), precision)
+    eng.set_members(0, members)
+    spad, lpad, d = util.layouts(50)
+    spad, lpad, d = spad[:n_layouts], lpad[:n_layouts], d[:n_layouts]
+    fit, lr, steps, st = eng.evaluate(spad, lpad, d, 2500)
+    want = po.evaluate(cfg.env_cfg(), sizes, 1, members.astype(eng.dtype), spad, lpad, d, 2500, precision, threads=8)
+    ep_steps, ep_flags, ep_fit = eng.read_episodes()
+    assert np.array_equal(ep_steps, want["ep_steps"])
+    assert np.array_equal(ep_flags, want["ep_flags"])
+    assert np.array_equal(ep_fit, want["ep_fit"])
+    assert np.array_equal(steps, want["steps"]) and np.array_equal(lr, want["lr"]) and np.array_equal(fit, want["fitness"])
+    assert st.sum_steps == want["steps"].sum() and st.members == len(members)
+    assert st.best_fitness == want["fitness"].min() and st.best_index == int(np.argmin(want["fitness"]))
+    eng.close()
+
+
+@pytest.mark.parametrize("topo", ["16_16", "16_64_32", "32_128_32", "8_16_32_16_8"])
+def test_generation_topologies_and_golden(ll, po, topo):
+    """Elites of the sample runs on the 50 balanced seed-5247 layouts: matches the fixtures produced by the
+    reference's own environment code (tests/golden/ref_outputs.json) and the oracle, fp64 and fp32."""
+    g = util.golden()["elite_runs"][topo]
+    e, sizes = util.elites(topo)
+    spad, lpad, d = util.layouts(50)
+    for precision in (64, 32):
+        eng, cfg = _engine(ll, sizes, 10, precision, cfg={k: v for k, v in g["extra"].items()})
+        eng.set_members(0, e)
+        fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
+        run = g["runs"][str(precision)]
+        assert fit[:2].tolist() == run["fitness"] and lr[:2].tolist() == run["lr"] and steps[:2].tolist() == run["steps"]
+        ep_steps, ep_flags, ep_fit = eng.read_episodes()
+        for m in range(2):
+            rows = np.array(run["per_layout"][m])
+            assert np.array_equal(ep_steps[m], rows[:, 0].astype(np.int64))
+            assert np.array_equal(ep_flags[m], rows[:, 1].astype(np.int64))
+            assert np.array_equal(ep_fit[m], rows[:, 2])
+        want = po.evaluate(cfg.env_cfg(), sizes, 1, e.astype(eng.dtype), spad, lpad, d, 5000, precision, threads=8)
+        assert np.array_equal(fit, want["fitness"])
+        eng.close()
+
+
+def test_sigmoid_activation_and_odd_topology(ll, po):
+    sizes = [5, 7, 13, 4]  # widths that are not multiples of 4: exercises the padded columns
+    members = util.random_population(sizes, 33, 5, scale=2.0)
+    spad, lpad, d = util.layouts(8)
+    for act in (0, 1):
+        for precision in (64, 32):
+            eng, cfg = _engine(ll, sizes, 33, precision, activation=act)
+            eng.set_members(0, members)
+            fit, lr, steps, _ = eng.evaluate(spad, lpad, d, 1200)
+            want = po.evaluate(cfg.env_cfg(), sizes, act, members.astype(eng.dtype), spad, lpad, d, 1200, precision, threads=8)
+            assert np.array_equal(fit, want["fitness"]) and np.array_equal(steps, want["steps"])
+            for m in (0, 9):
+                s = np.array([0.3, -1.2, 0.05, -0.1, 0.7])
+                assert eng.feedforward_index(s, m) == po.forward(sizes, act, members[m].astype(eng.dtype), s.astype(eng.dtype), precision)
+            eng.close()
+
+
+def test_reward_shaping_variants(ll, po):
+    """Non-default sp_*/tp_* values (the keys the sample configs vary) and a short max_steps."""
+    sizes = util.TOPOLOGIES["16_16"]
+    pe, _ = util.elite_population("16_16", 24, 9)
+    members = np.concatenate([pe, util.random_population(sizes, 24, 2)])
+    ov = {"NNTrainingCfg.tp_landed_bonus": 250.0, "NNTrainingCfg.tp_crashed_penalty": 75.5, "NNTrainingCfg.tp_no_fuel_penalty": 500.0,
+          "NNTrainingCfg.tp_landed_lr_bonus": 1234.5, "NNTrainingCfg.sp_action_factor": 0.02, "PlanetCfg.g": 0.06, "GameCfg.max_vy": -2.5}
+    spad, lpad, d = util.layouts(50)
+    for precision in (64, 32):
+        for max_steps in (1, 40, 1500):
+            eng, cfg = _engine(ll, sizes, len(members), precision, cfg=ov)
+            eng.set_members(0, members)
+            fit, lr, steps, _ = eng.evaluate(spad, lpad, d, max_steps)
+            want = po.evaluate(cfg.env_cfg(), sizes, 1, members.astype(eng.dtype), spad, lpad, d, max_steps, precision, threads=8)
+            assert np.array_equal(fit, want["fitness"]) and np.array_equal(lr, want["lr"]) and np.array_equal(steps, want["steps"])
+            eng.close()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# 4. GA kernels
+@pytest.mark.parametrize("precision", [64, 32])
+def test_create_population_bit_exact(ll, po, precision):
+    sizes = util.TOPOLOGIES["8_16_8"]
+    pop, top = 301, 10
+    eng, cfg = _engine(ll, sizes, pop, precision, top=top, seed=5247)
+    eng.set_population_strategy(2, 0.35)
+    eng.create_population(True)  # initial: N(0, 1)
+    got0 = eng.get_members(0, pop)
+    want0 = po.create_population(sizes, 5247, pop, top, 0, 2, 0.35, True, False, 1.0, 0.1, np.zeros((pop, eng.P)), precision)
+    assert np.array_equal(got0, want0)
+    assert abs(got0.std() - 1.0) < 0.02 and abs(got0.mean()) < 0.02
+    # children of the first `top` members (as if they had won), generation key = epochs + 1
+    eng.mark_elites()
+    eng.set_epochs(6)
+    eng.create_population(True)
+    got1 = eng.get_members(0, pop)
+    want1 = po.create_population(sizes, 5247, pop, top, 7, 2, 0.35, True, True, 1.0, 0.1, got0, precision)
+    assert np.array_equal(got1, want1)
+    assert np.array_equal(got1[:top], got0[:top])  # elitism
+    n_inject = int(np.floor(0.35 * (pop - top) + 0.5))
+    assert abs(got1[pop - n_inject:].std() - 1.0) < 0.03
+    # no elitism, all-from-elites strategy
+    eng.set_population_strategy(1, 0.0)
+    eng.create_population(False)
+    got2 = eng.get_members(0, pop)
+    want2 = po.create_population(sizes, 5247, pop, top, 7, 1, 0.0, False, True, 1.0, 0.1, got0, precision)
+    assert np.array_equal(got2, want2)
+    eng.close()
+
+
+def test_topk_with_ties_and_select(ll, po):
+    sizes = util.TOPOLOGIES["8_16_8"]
+    pop, top = 5000, 37
+    eng, cfg = _engine(ll, sizes, pop, 64, top=top)
+    eng.create_population(True)  # random nets: many of them crash identically -> exact fitness ties
+    spad, lpad, d = util.layouts(8)
+    fit, lr, steps, st = eng.evaluate(spad[:2], lpad[:2], d[:2], 300)
+    assert len(np.unique(fit)) < pop  # ties are present
+    want = po.topk(fit, top)
+    f, idx = eng.local_topk()
+    assert np.array_equal(idx, want) and np.array_equal(f, fit[want])
+    before = eng.get_members(0, pop)
+    elites = eng.select(None)
+    assert np.array_equal(elites, want)
+    eng.create_population(True)
+    after = eng.get_members(0, top)
+    assert np.array_equal(after, before[want.astype(np.int64)])  # UpdateWeightsAndBiases: winners in rank order at slots 0..top-1
+    # host-sorted variant (the reference's std::sort result handed over)
+    order = np.argsort(fit, kind="stable").astype(np.uint64)
+    assert np.array_equal(eng.select(order), order[:top])
+    eng.close()
+
+
+def test_step_generation_matches_split_calls(ll, po):
+    sizes = util.TOPOLOGIES["16_16"]
+    spad, lpad, d = util.layouts(8)
+    outs = []
+    for fused in (False, True):
+        eng, cfg = _engine(ll, sizes, 200, 64)
+        eng.set_population_strategy(2, 0.35)
+        eng.create_population(True)
+        eng.set_layouts(spad, lpad, d)
+        for _ in range(3):
+            if fused:
+                eng.step_generation(400, True)
+            else:
+                eng.evaluate_device(400)
+                eng.select(None)
+                eng.create_population(True)
+                eng.update_epochs(1)
+        assert eng.get_epochs() == 3
+        outs.append(eng.get_members(0, 200))
+        eng.close()
+    assert np.array_equal(outs[0], outs[1])
+
+
+# 5. sharding: two ranks (emulated as two contexts on this GPU) reproduce the single-shard generation exactly
+def test_two_shards_equal_one(ll, po):
+    import torch
+    sizes = util.TOPOLOGIES["8_16_8"]
+    pop, top = 203, 10
+    spad, lpad, d = util.layouts(8)
+    one, cfg = _engine(ll, sizes, pop, 64, top=top)
+    one.set_population_strategy(2, 0.35)
+    one.create_population(True)
+    f1, _, s1, _ = one.evaluate(spad, lpad, d, 500)
+    e1 = one.select(None)
+    one.create_population(True)
+    shards = [ll.Engine(cfg, population=pop, top=top, precision=64, rank=r, world=2) for r in range(2)]
+    fit, cands = [], []
+    for sh in shards:
+        sh.set_population_strategy(2, 0.35)
+        sh.create_population(True)
+        f, _, s, _ = sh.evaluate(spad, lpad, d, 500)
+        fit.append(f)
+        cands.append(sh.local_topk())
+    assert np.array_equal(np.concatenate(fit), f1)
+    cf = np.concatenate([c[0] for c in cands])
+    ci = np.concatenate([c[1] for c in cands])
+    order = np.lexsort((ci, cf))[:top]
+    elite_idx = ci[order]
+    assert np.array_equal(elite_idx, e1)
+    bufs = []
+    for sh in shards:
+        b = torch.zeros(sh.elite_buffer_bytes() // 8, dtype=torch.int64, device="cuda")
+        torch.cuda.synchronize()
+        sh.gather_elites(elite_idx, b.data_ptr())
+        sh.synchronize()
+        bufs.append(b)
+    total = bufs[0] + bufs[1]  # what an NCCL all-reduce(SUM) over the bit patterns produces
+    torch.cuda.synchronize()
+    for sh in shards:
+        sh.set_elites(total.data_ptr())
+        sh.create_population(True)
+        sh.synchronize()
+    got = np.concatenate([sh.get_members(sh.first_global, sh.pop_local) for sh in shards])
+    assert np.array_equal(got, one.get_members(0, pop))
+    for e in shards + [one]:
+        e.close()
+
+
+# 6. weight file
+def test_weight_file_roundtrip(ll, po, tmp_path):
+    sample = util.GOLDEN + "/sample_lunar_lander_5_8_16_8_4_s_0500.txt"
+    hdr = ll.peek_weight_file(sample)
+    assert hdr["sizes"] == [5, 8, 16, 8, 4] and hdr["top"] == 10 and hdr["population"] == 100 and hdr["epochs"] == 500
+    e, sizes = util.elites("8_16_8")
+    eng, cfg = _engine(ll, sizes, 100, 64)
+    eng.deserialize(sample)
+    assert eng.get_epochs() == 500
+    eng.select(np.arange(100, dtype=np.uint64))  # UpdateWeightsAndBiases with the identity order: elites stay
+    assert np.array_equal(eng.get_members(0, 10), e)
+    out = str(tmp_path / "lunar_lander_last.txt")
+    eng.serialize(out, "lunar_lander")
+    a = open(sample).read().split()
+    b = open(out).read().split()
+    g = a.index("generator")
+    assert a[:g] == b[:g], "everything before the generator line is reproduced token for token"
+    assert len(b) - b.index("generator") - 1 == 624
+    # the non-elite slots were regenerated from the elites with the stored epoch count as generation key
+    want = po.create_population(sizes, 5247, 100, 10, 500, 2, hdr["ratio"], True, True, 1.0, 0.1, np.concatenate([e, np.zeros((90, eng.P))]), 64)
+    assert np.array_equal(eng.get_members(0, 100), want)
+    eng.close()
+
+
+# 7. fast fp32 mode: judged on outcomes, not sequences
+def test_fast_mode_outcomes(ll, po):
+    topo = "16_64_32"
+    members, sizes = util.elite_population(topo, 256, 4, noise=0.02)
+    spad, lpad, d = util.layouts(50)
+    eng, cfg = _engine(ll, sizes, 256, 32, mode=1)
+    eng.set_members(0, members)
+    fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
+    _, flags, _ = eng.read_episodes()
+    want = po.evaluate(cfg.env_cfg(), sizes, 1, members.astype(np.float32), spad, lpad, d, 5000, 32, threads=8)
+    rate_gpu, rate_cpu = (flags & 4).astype(bool).mean(), (want["ep_flags"] & 4).astype(bool).mean()
+    assert abs(rate_gpu - rate_cpu) <= 0.02, (rate_gpu, rate_cpu)                       # landed-successfully rate within 2 points
+    assert abs(steps.sum() - want["steps"].sum()) <= 0.02 * want["steps"].sum()         # total steps within 2 %
+    scale = np.abs(want["fitness"]).mean()
+    assert abs(fit.mean() - want["fitness"].mean()) <= 0.03 * scale                     # mean fitness within 3 % of its magnitude
+    eng.close()
+
+
+# 8. BASELINE.json configs at full size
+def test_config2_full_size(ll, po):
+    """configs[1]: 8_16_8, population 4096, single start position — the oracle is fast enough to check everything."""
+    members, sizes = util.elite_population("8_16_8", 4096, 21)
+    members[2048:] = util.random_population(sizes, 2048, 22)
+    spad, lpad, d = util.layouts(1)
+    for precision in (64, 32):
+        eng, cfg = _engine(ll, sizes, 4096, precision)
+        eng.set_members(0, members)
+        fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
+        want = po.evaluate(cfg.env_cfg(), sizes, 1, members.astype(eng.dtype), spad, lpad, d, 5000, precision, threads=8)
+        assert np.array_equal(fit, want["fitness"]) and np.array_equal(steps, want["steps"])
+        assert np.array_equal(eng.select(None), po.topk(want["fitness"], 10))
+        eng.close()
+
+
+def test_config3_properties_and_sample(ll, po):
+    """configs[2]: 16_64_32, population 65536 x 8 start positions.  Full population on the GPU; a strided sample of
+    members is compared bit-exactly with the oracle, the rest through invariants."""
+    sizes = util.TOPOLOGIES["16_64_32"]
+    pop = 65536
+    eng, cfg = _engine(ll, sizes, pop, 32, top=10)
+    eng.set_population_strategy(2, 0.35)
+    eng.create_population(True)
+    e, _ = util.elites("16_64_32")
+    eng.set_members(0, e)
+    eng.mark_elites()
+    eng.create_population(True)  # elites + mutated children + 35 % random injection
+    spad, lpad, d = util.layouts(8)
+    fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
+    ep_steps, ep_flags, ep_fit = eng.read_episodes()
+    assert ep_steps.min() >= 9 and ep_steps.max() <= 5000            # nothing touches down before step 9 from y0 = 433.8
+    assert np.array_equal(steps, ep_steps.sum(axis=1).astype(np.float64))
+    assert st.sum_steps == steps.sum()
+    timeout = ep_steps == 5000
+    assert np.all((ep_flags[timeout] & 1) == 0) or np.all(ep_steps[(ep_flags & 1) == 0] == 5000)
+    assert np.all(((ep_flags & 4) == 0) | ((ep_flags & 2) == 0))     # success and crashed are exclusive
+    pick = np.arange(0, pop, 257)
+    sub = eng.get_members(0, pop)[pick]
+    want = po.evaluate(cfg.env_cfg(), sizes, 1, sub, spad, lpad, d, 5000, 32, threads=8)
+    assert np.array_equal(fit[pick], want["fitness"]) and np.array_equal(steps[pick], want["steps"])
+    assert np.array_equal(eng.select(None), po.topk(fit, 10))
+    eng.close()
