@@ -1,0 +1,446 @@
+#!/usr/bin/env python
+"""bench.py — lander-steps/sec and generations/sec of the neuro-evolution hot path (BASELINE.json `metric`).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c4|c2|c3|c1] [--impl reference]
+
+A "step" is one generation over one batch of synthetic input: evaluate every (member, layout) episode of the
+population (K1), select the elites (K2/K3) and breed the next population (K4).  One JSON line is printed by rank 0.
+
+Workloads (`--workload`):
+  c4  (default) BASELINE.json configs[3]: 32_128_32, 131072 members PER GPU (= the 1M population at 8 GPUs; weak
+      scaling), config.txt's 50 layouts, S-elite population (sample-run elites + N(0, 0.05^2), Philox on the device),
+      fp32 fast mode — the configuration the metric's target is stated on
+  c2  configs[1]: 8_16_8, population 4096, single start position          (working set < L2: L2 is flushed between steps)
+  c3  configs[2]: 16_64_32, population 65536 x 8 start positions
+  c1  configs[0]: default config.txt (16_16, population 100, 50 layouts), fp64 exact mode
+Keys beyond the base contract: `roofline` (episode kernel against the FP32/FP64 FMA peak measured on this GPU, see
+DESIGN.md §Measurement), `roofline_ga` (breed kernel against the measured HBM copy bandwidth), `cpu_baseline`
+(the reference's own train_generation, oracle/_ref, on this box's host cores over a bounded sample), `e2e`
+(the same generations driven through the reference-facing calls with HOST buffers).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+TOPOLOGIES = {
+    "16_16": [5, 16, 16, 4], "8_16_8": [5, 8, 16, 8, 4], "16_64_32": [5, 16, 64, 32, 4],
+    "32_128_32": [5, 32, 128, 32, 4], "8_16_32_16_8": [5, 8, 16, 32, 16, 8, 4],
+}
+# name -> (topology, members per GPU, layouts, precision, mode, scaling, description)
+WORKLOADS = {
+    "c4": ("32_128_32", 131072, 50, 32, 1, "weak",
+           "configs[3]: 32_128_32, 131072 members/GPU (1M at 8 GPUs) x 50 layouts, S-elite, fp32 fast"),
+    "c3": ("16_64_32", 65536, 8, 32, 1, "weak", "configs[2]: 16_64_32, population 65536/GPU x 8 start positions, S-elite, fp32 fast"),
+    "c2": ("8_16_8", 4096, 1, 32, 1, "weak", "configs[1]: 8_16_8, population 4096/GPU, single start position, S-elite, fp32 fast"),
+    "c1": ("16_16", 100, 50, 64, 0, "weak", "configs[0]: config.txt defaults, 16_16, population 100/GPU x 50 layouts, S-elite, fp64 exact"),
+}
+L2_BYTES = 126 << 20
+SIGMA_MUT = 0.05
+
+
+def flop_per_step(sizes):
+    mac = sum(sizes[i] * sizes[i + 1] for i in range(len(sizes) - 1))
+    return 2 * mac + sum(sizes[1:])
+
+
+def load_elites(topo):
+    z = np.load(os.path.join(ROOT, "tests", "golden", f"elites_{topo}.npz"))
+    return z["params"]
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc, self.thread = index, [], None, None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return
+        self.thread = threading.Thread(target=self._read, daemon=True)
+        self.thread.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        self.thread.join(timeout=5)
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0])), mx.append(float(r[1])), pw.append(float(r[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "power_w_max": float(max(pw)), "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# CPU side: the reference's own train_generation (src/nn_engine_trainer.cpp:443-539, compiled unchanged into
+# oracle/_ref by oracle/Makefile) on this box's host cores.  Only this leg and --impl reference touch oracle/.
+def s_elite_sample(topo, n, seed):
+    e = load_elites(topo)
+    rng = np.random.default_rng(seed)
+    return e[np.arange(n) % e.shape[0]] + rng.normal(scale=SIGMA_MUT, size=(n, e.shape[1]))
+
+
+def cpu_layouts(n_layouts):
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import pyoracle as po
+    if po.ref() is not None:
+        return po.ref_make_layouts(os.path.join(ROOT, "config.txt"), 5247, n_layouts)
+    raise RuntimeError("oracle/_ref is not built (it is compiled where /root/reference exists and travels prebuilt)")
+
+
+def cpu_reference_pass(topo, n_layouts, precision, members, layouts, max_steps=5000):
+    """One pass of the reference CPU path over `members`; returns (lander steps, seconds, threads)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import pyoracle as po
+    sizes = TOPOLOGIES[topo]
+    spad, lpad, d = layouts
+    r = po.ref_evaluate(os.path.join(ROOT, "config.txt"), sizes, 1, members, spad, lpad, d, max_steps, precision, fast=True)
+    return float(r["steps"].sum()), float(r["seconds"]), po.ref_threads()
+
+
+def cpu_calibrate(topo, n_layouts, precision, target_s, seed=99):
+    """Pick a member count whose reference pass takes about `target_s` seconds on all host threads."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import pyoracle as po
+    threads = max(1, po.ref_threads())
+    layouts = cpu_layouts(n_layouts)
+    n0 = threads
+    while True:  # grow the probe until fixed costs (thread pool, simulator construction) stop dominating it
+        steps0, sec0, _ = cpu_reference_pass(topo, n_layouts, precision, s_elite_sample(topo, n0, seed), layouts)
+        if sec0 >= 0.4 or n0 >= (1 << 15):
+            break
+        n0 *= 4
+    per_member = max(sec0, 1e-4) / n0
+    n = int(max(threads, min(1 << 16, round(target_s / per_member / threads) * threads)))
+    return n, layouts, threads
+
+
+def cpu_baseline(topo, n_layouts, precision, target_s=15.0):
+    n, layouts, threads = cpu_calibrate(topo, n_layouts, precision, target_s)
+    steps, sec, _ = cpu_reference_pass(topo, n_layouts, precision, s_elite_sample(topo, n, 100), layouts)
+    return {"value": steps / sec, "unit": "lander-steps/s", "cores": threads, "kind": "reference",
+            "sample": f"{n} S-elite members x {n_layouts} layouts of the same workload ({int(steps)} lander steps in {sec:.2f} s), "
+                      f"reference train_generation compiled unchanged (oracle/_ref, g++ -O3 -mavx2 -ffp-contract=off), "
+                      f"T={'double' if precision == 64 else 'float'}, policy network from the ma-libs stand-in (oracle/shim)"}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path, all host threads, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    topo, per_gpu, n_layouts, precision, mode, scaling, desc = WORKLOADS[args.workload]
+    n_layouts = args.layouts or n_layouts
+    try:
+        n, layouts, threads = cpu_calibrate(topo, n_layouts, precision, args.ref_step_seconds)
+    except Exception as e:  # the prebuilt oracle/_ref did not travel
+        print(json.dumps({"impl": "reference", "unavailable": str(e).splitlines()[0][:200]}))
+        return
+    tot_steps, tot_sec = 0.0, 0.0
+    for it in range(args.warmup + args.steps):
+        members = s_elite_sample(topo, n, 1000 + it)
+        steps, sec, _ = cpu_reference_pass(topo, n_layouts, precision, members, layouts)
+        if it >= args.warmup:
+            tot_steps += steps
+            tot_sec += sec
+    value = tot_steps / tot_sec
+    sample = (f"each step = reference train_generation over {n} S-elite members x {n_layouts} layouts "
+              f"({int(tot_steps / args.steps)} lander steps/step), {threads} host threads")
+    line = {
+        "impl": "reference", "metric": "lander-steps/sec", "value": value, "unit": "lander-steps/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_sec / args.steps, "higher_is_better": True,
+        "scaling": scaling, "vs_baseline": None, "dtype": "f64" if precision == 64 else "f32", "data": "synthetic",
+        "config": {"workload": desc, "topology": topo, "layouts": n_layouts, "max_steps": 5000, "members_per_step": n},
+        "cpu_baseline": {"value": value, "unit": "lander-steps/s", "cores": threads, "kind": "reference", "sample": sample},
+        "e2e": {"value": value, "unit": "lander-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "generations_per_sec_at_full_population": value / (tot_steps / args.steps / n * per_gpu * max(1, args.gpus)),
+    }
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------------------------
+def measured_hbm_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+        except Exception:
+            pass
+    return 6650.0, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
+
+
+def ncu_traffic(workload):
+    """DRAM bytes per launch of the episode kernel from the committed ncu --set full capture, if there is one."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get(workload)
+        except Exception:
+            return None
+    return None
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+
+    import lunar_lander_b200 as ll
+    from lunar_lander_b200 import _abi
+    from lunar_lander_b200.sharded import ShardedGeneration
+    import ctypes as C
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — this framework has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    if args.gpus != world and rank == 0:
+        print(f"bench.py: --gpus {args.gpus} but WORLD_SIZE={world}; using {world}", file=sys.stderr)
+
+    topo, per_gpu, n_layouts, precision, mode, scaling, desc = WORKLOADS[args.workload]
+    per_gpu = args.pop_per_gpu or per_gpu
+    n_layouts = args.layouts or n_layouts
+    if args.precision:
+        precision, mode = args.precision, (0 if args.precision == 64 or args.exact else 1)
+    elif args.exact:
+        mode = 0
+    sizes = TOPOLOGIES[topo]
+    top = 10
+    cfg = ll.Config(os.path.join(ROOT, "config.txt"), {"NNConfig.hlayers": ",".join(str(s) for s in sizes[1:-1])})
+    max_steps = cfg.getInt("GameCfg.max_steps")
+    spad, lpad, dirs, _, _ = ll.make_layouts(cfg, 5247, n_layouts)
+
+    # roofline denominators measured on THIS device before anything else runs on it (rank-local)
+    fma_burst, fma_sust, mhz_b, mhz_s = C.c_double(), C.c_double(), C.c_double(), C.c_double()
+    pcode = 64 if precision == 64 else 32
+    _abi.check(_abi.lib.ll_microbench_fma(local_rank, pcode, 0.25, C.byref(fma_burst), C.byref(mhz_b)))
+    _abi.check(_abi.lib.ll_microbench_fma(local_rank, pcode, 3.0, C.byref(fma_sust), C.byref(mhz_s)))
+
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    eng = ll.Engine(cfg, sizes=sizes, population=per_gpu * world, top=top, precision=precision, mode=mode, rank=rank, world=world,
+                    device=local_rank, seed=5247, sigma_mut=SIGMA_MUT)
+    eng.set_stream(stream.cuda_stream)
+    sg = ShardedGeneration(eng)
+
+    # ---- synthetic S-elite population, generated on the device: parents = the sample run's elites (rank 0 owns slots
+    # [0, top)), children = parent + N(0, 0.05^2) by Philox (K4); the timed generations then use config.txt's strategy
+    elites = load_elites(topo)[:top]
+    if rank == 0:
+        eng.set_members(0, elites)
+    eng.gather_elites(np.arange(top, dtype=np.uint64), sg.elite_buf.data_ptr())
+    if world > 1:
+        dist.all_reduce(sg.elite_buf)
+    eng.set_elites(sg.elite_buf.data_ptr())
+    eng.set_population_strategy(1, 0.0)
+    eng.create_population(True)
+    eng.set_population_strategy(2, cfg.getDouble("NNConfig.random_injection_ratio"))
+    eng.set_layouts(spad, lpad, dirs)
+    eng.synchronize()
+
+    row_bytes = int(eng.info.params_padded) * (8 if precision == 64 else 4)
+    working_set = eng.pop_local * row_bytes
+    flush = working_set < 2 * L2_BYTES
+    flush_buf = torch.empty(512 << 20, dtype=torch.uint8, device="cuda") if flush else None
+
+    def generation():
+        if world == 1:
+            eng.step_generation(max_steps, True, want_stats=False)
+        else:
+            sg.step(max_steps, True)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        generation()
+    barrier()
+    eng.step_counter(reset=True)
+    eng.kernel_times(reset=True)
+    eng.profile(True)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    t_wall0 = time.perf_counter()
+    for k in range(args.steps):
+        if flush:
+            flush_buf.fill_(k & 255)
+        ev[k][0].record(stream)
+        generation()
+        ev[k][1].record(stream)
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    clocks = sampler.stop() if rank == 0 else None
+    ms_total = sum(a.elapsed_time(b) for a, b in ev)
+    steps_local, n_eval = eng.step_counter(reset=True)
+    kt = eng.kernel_times(reset=True)
+    eng.profile(False)
+    t = torch.tensor([ms_total, kt.episode_ms], dtype=torch.float64, device="cuda")
+    s = torch.tensor([steps_local], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(s, op=dist.ReduceOp.SUM)
+    ms_total_max, episode_ms_max = float(t[0]), float(t[1])
+    steps_global = float(s[0])
+    launches = int(kt.episode_launches + kt.select_launches + kt.gather_launches + kt.mutate_launches + kt.other_launches)
+
+    # ---- e2e: the same generations driven the way the reference's train() drives them (src/nn_engine_trainer.cpp:373-407)
+    # with HOST buffers: layouts go in from host memory, fitness / lr / steps come back to host vectors, the host sorts the
+    # indices (std::sort in the reference) and hands the order to UpdateWeightsAndBiases.  Copies are inside the timed region.
+    e2e_steps = args.e2e_steps if args.e2e_steps is not None else args.steps
+    out = (np.empty(eng.pop_local), np.empty(eng.pop_local), np.empty(eng.pop_local))
+    h2d = d2h = 0
+    e2e_lander_steps = 0.0
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(e2e_steps):
+        fit, lr, st_steps, st = eng.evaluate(spad, lpad, dirs, max_steps, out=out)
+        h2d += n_layouts * 16
+        d2h += 3 * 8 * eng.pop_local + 48
+        e2e_lander_steps += float(st_steps.sum())
+        if world == 1:
+            order = np.argsort(fit, kind="stable").astype(np.uint64)
+            eng.select(order)
+            h2d += 8 * top
+            eng.create_population(True)
+            eng.update_epochs(1)
+        else:
+            b0, b1 = sg.h2d_bytes, sg.d2h_bytes
+            sg.select_and_breed(True)
+            h2d += sg.h2d_bytes - b0
+            d2h += sg.d2h_bytes - b1
+    barrier()
+    e2e_sec = time.perf_counter() - t0
+    t = torch.tensor([e2e_sec], dtype=torch.float64, device="cuda")
+    s = torch.tensor([e2e_lander_steps], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(s, op=dist.ReduceOp.SUM)
+    e2e_sec, e2e_lander_steps = float(t[0]), float(s[0])
+
+    if rank == 0:
+        fps = flop_per_step(sizes)
+        value = steps_global / (ms_total_max * 1e-3)
+        achieved = (steps_local * fps) / (episode_ms_max * 1e-3) / 1e12 if episode_ms_max > 0 else 0.0
+        long_kernel = episode_ms_max / max(1, args.steps) > 250.0
+        peak = fma_sust.value if long_kernel else fma_burst.value
+        hbm_peak, hbm_src = measured_hbm_peak()
+        elt = 8 if precision == 64 else 4
+        ga_bytes = ((eng.pop_local - top) * int(eng.info.params_padded) * elt + top * int(eng.info.params_padded) * elt) * args.steps
+        ga_gbs = ga_bytes / (kt.mutate_ms * 1e-3) / 1e9 if kt.mutate_ms > 0 else 0.0
+        line = {
+            "metric": "lander-steps/sec", "value": value, "unit": "lander-steps/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_total_max / args.steps, "higher_is_better": True, "scaling": scaling,
+            "vs_baseline": None, "dtype": "f64" if precision == 64 else "f32", "data": "synthetic",
+            "config": {"workload": desc, "topology": topo, "population": per_gpu * world, "population_per_gpu": per_gpu,
+                       "layouts": n_layouts, "max_steps": max_steps, "mode": "exact" if mode == 0 else "fast",
+                       "strategy": "MIXED_WITH_RANDOM_INJECTION 0.35, elitism, top 10, sigma_mut 0.05",
+                       "l2": "L2 flushed (512 MiB write) between timed steps" if flush else
+                             f"per-GPU working set {working_set / 1e6:.0f} MB of member rows > 126 MB L2, no flush needed",
+                       "kernel": eng.info.kernel.decode()},
+            "generations_per_sec": args.steps / (ms_total_max * 1e-3),
+            "lander_steps_per_generation": steps_global / args.steps,
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "roofline": {"bound": "fp64_fma" if precision == 64 else "fp32_fma", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                         "frac": achieved / peak if peak > 0 else None, "traffic": ncu_traffic(args.workload),
+                         "kernel": eng.info.kernel.decode(), "flop_per_lander_step": fps,
+                         "kernel_ms_per_launch": episode_ms_max / max(1, args.steps),
+                         "kernel_share_of_step": episode_ms_max / ms_total_max if ms_total_max > 0 else None,
+                         "peak_source": ("FMA microbenchmark on this GPU (ll_microbench_fma), " +
+                                         ("sustained 3 s loop" if long_kernel else "0.25 s burst") + ", of measured"),
+                         "peak_burst": fma_burst.value, "peak_sustained": fma_sust.value,
+                         "sm_mhz_during_peak": mhz_s.value if long_kernel else mhz_b.value,
+                         "peak_nominal_1965mhz": (148 * 128 * 2 * 1.965e9 / 1e12) if precision == 32 else None},
+            "roofline_ga": {"bound": "hbm", "achieved": ga_gbs, "peak": hbm_peak, "unit": "GB/s",
+                            "frac": ga_gbs / hbm_peak if hbm_peak else None, "traffic": None, "kernel": "ll_create_population_kernel",
+                            "kernel_ms_per_launch": kt.mutate_ms / max(1, kt.mutate_launches), "peak_source": hbm_src},
+            "kernel_ms": {"episode": kt.episode_ms, "select": kt.select_ms, "gather": kt.gather_ms, "breed": kt.mutate_ms,
+                          "wall_s_timed_region": t_wall},
+            "e2e": {"value": e2e_lander_steps / e2e_sec if e2e_sec > 0 else 0.0, "unit": "lander-steps/s",
+                    "h2d_bytes_per_step": h2d / max(1, e2e_steps), "d2h_bytes_per_step": d2h / max(1, e2e_steps), "steps": e2e_steps,
+                    "generations_per_sec": e2e_steps / e2e_sec if e2e_sec > 0 else 0.0,
+                    "api": "ll_evaluate(host layouts -> host fitness/lr/steps) + host argsort + ll_select + ll_create_population"},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            try:
+                line["cpu_baseline"] = cpu_baseline(topo, n_layouts, precision, args.cpu_seconds)
+            except Exception as e:
+                line["cpu_baseline"] = {"value": None, "unit": "lander-steps/s", "cores": 0, "kind": "reference",
+                                        "sample": f"unavailable: {str(e).splitlines()[0][:160]}"}
+        print(json.dumps(line))
+    eng.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
+    ap.add_argument("--pop-per-gpu", type=int, default=0)
+    ap.add_argument("--layouts", type=int, default=0)
+    ap.add_argument("--precision", type=int, default=0, choices=[0, 32, 64])
+    ap.add_argument("--exact", action="store_true", help="LL_MODE_EXACT (bit-exact operation order) instead of the fast fp32 mode")
+    ap.add_argument("--e2e-steps", type=int, default=None)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--ref-step-seconds", type=float, default=8.0)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

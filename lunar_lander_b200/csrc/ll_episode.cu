@@ -181,7 +181,7 @@ namespace
 
         const int G = a.G, L = a.n_layouts;
         const int slot = lane / G, j = lane - slot * G;
-        const T* wrow  = wsm + (size_t)slot * a.slot_stride;
+        const T* wrow  = wsm + (size_t)min(slot, a.nslots - 1) * a.slot_stride; // surplus lane groups (slot >= nslots) idle
         const ll_layout<T>* layouts = static_cast<const ll_layout<T>*>(a.layouts);
         const uint32_t row_bytes    = (uint32_t)tp.p_dev * sizeof(T);
 
@@ -377,6 +377,9 @@ namespace
             while (G < L) G <<= 1;
         }
         a.G = G, a.nslots = 32 / G;
+        // a warp never stages more than ~48 KB of member rows: with few layouts and wide networks the tile holds
+        // fewer members than the warp has lane groups, and the surplus lanes idle
+        while (a.nslots > 1 && (size_t)a.nslots * tp.p_dev * sizeof(T) > (size_t)48 << 10) a.nslots >>= 1;
         a.n_tiles = (unsigned int)((h.n_members + a.nslots - 1) / a.nslots);
         // member rows in shared memory: pitch == 4 words (mod 32) so that 16-byte reads of the same element by
         // lanes of different members fall into different bank groups
