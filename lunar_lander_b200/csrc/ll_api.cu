@@ -491,6 +491,7 @@ extern "C" int ll_set_layouts(ll_ctx* ctx, const int32_t* spad_x1, const int32_t
     LL_CUDA(ctx, cudaMemcpyAsync(ctx->d_layouts, ctx->h_pin, lay_bytes * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
     LL_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->n_layouts = n;
+    std::snprintf(ctx->kernel_name, sizeof(ctx->kernel_name), "%s", ll_episode_kernel_name(ctx, n));
     return LL_OK;
 }
 

@@ -433,7 +433,11 @@ namespace
 int ll_launch_episode(ll_ctx* ctx, const ll_episode_args& a)
 {
     if (ctx->precision == 64) return launch_t<double, LL_MODE_EXACT>(ctx, a);
-    if (ctx->mode == LL_MODE_FAST) return launch_t<float, LL_MODE_FAST>(ctx, a);
+    if (ctx->mode == LL_MODE_FAST)
+    { // the team kernel needs weight reuse across layouts; traces and tiny layout counts stay lane-per-episode
+        if (a.trace == nullptr && a.n_layouts >= 4) return ll_launch_episode_fast(ctx, a);
+        return launch_t<float, LL_MODE_FAST>(ctx, a);
+    }
     return launch_t<float, LL_MODE_EXACT>(ctx, a);
 }
 
@@ -444,8 +448,9 @@ int ll_launch_feedforward(ll_ctx* ctx, const void* member_row, const void* d_sta
     return launch_ff<float, LL_MODE_EXACT>(ctx, member_row, d_state, d_action);
 }
 
-const char* ll_episode_kernel_name(const ll_ctx* ctx, int)
+const char* ll_episode_kernel_name(const ll_ctx* ctx, int n_layouts)
 {
     if (ctx->precision == 64) return "ll_episode_kernel<double,exact>";
-    return ctx->mode == LL_MODE_FAST ? "ll_episode_kernel<float,fast>" : "ll_episode_kernel<float,exact>";
+    if (ctx->mode == LL_MODE_FAST) return n_layouts >= 4 ? "ll_episode_fast_kernel (team GEMM)" : "ll_episode_kernel<float,fast>";
+    return "ll_episode_kernel<float,exact>";
 }

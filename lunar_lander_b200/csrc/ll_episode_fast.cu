@@ -1,0 +1,464 @@
+// ll_episode_fast.cu — K1 fast (fp32, LL_MODE_FAST): the throughput variant of the fused episode kernel.
+//
+// Replaces the same reference code as ll_episode.cu (train_generation / sim_task src/nn_engine_trainer.cpp:443-539,
+// GameLogicCpp<T> src/game_logic.cpp:124-388, the ma-libs feedforward call :501-502), with free summation order,
+// fused multiply-add and tanh.approx.f32 — judged on outcome rates, not on bit patterns (tests/test_gpu_parity.py).
+//
+// Why a different mapping: a lane-per-episode GEMV delivers one shared-memory word per FMA and
+// shared memory returns 32 words/clk/SM against 128 FMA lanes/clk/SM, i.e. <= 25 % of the FP32 pipe.  All L layouts of
+// a member share its weights, so one forward pass for a member is a small GEMM  D[S x out] = A[S x in] * W^T[in x out]
+// (S = concurrent episode slots).  A TEAM of threads owns one member at a time; each thread computes a register tile of
+// E episodes x 8 outputs (E*8 FMAs per E+8 words fetched), layers wide in K are split over k-slices and reduced
+// through shared memory.  Per step: env phase (one thread per slot: argmax -> lander update -> penalties -> next
+// state) then one phase per layer, separated by CTA barriers.  A member's row is staged once by a TMA bulk copy
+// (cp.async.bulk + mbarrier); teams pull members from a global queue, slots pull the member's layouts from a
+// shared-memory counter, so episode lengths of 9..max_steps steps balance dynamically.
+#include "ll_env.cuh"
+
+namespace
+{
+    constexpr int FO          = 8;   // outputs per thread tile
+    constexpr int MAX_THREADS = 256; // per CTA
+    constexpr int MAX_RES     = 256; // layouts whose per-episode results are kept in shared memory
+
+    struct fast_layer
+    {
+        int in, out, out_pad, w_off, b_off; // topology (element offsets inside a member row)
+        int nog, tiles, ks, klen;           // output groups, (episode group x output group) tiles, k-slices, k per slice
+        int in_off, out_off;                // element offsets of the activation buffers inside the team's region
+        int last;                           // output layer: always leaves pre-activation partial sums for the env phase
+    };
+
+    struct fast_args
+    {
+        const float* params;
+        const ll_layout<float>* layouts;
+        int n_layouts, max_steps;
+        unsigned long long n_members;
+        double *fitness, *lr, *steps;
+        int* ep_steps;
+        double* ep_fit;
+        unsigned int* queue;
+        int n_layers, act, p_dev;
+        int TS, NT, Ge, S;                                     // threads per team, teams per CTA, episode groups, slots = E * Ge
+        int part_off;                                          // element offset of the split-K partial buffer
+        int off_w, off_act, off_slot, off_res, team_bytes;     // byte offsets inside a team's shared-memory region
+        int res_in_smem;
+        fast_layer layer[LL_MAX_LAYERS];
+    };
+
+    // per-team control words (ints at byte 16 of the team region)
+    enum
+    {
+        C_NEXT_LAYOUT = 0,
+        C_N_ACTIVE    = 1,
+        C_HAS_MEMBER  = 2,
+        C_MEMBER_LO   = 3,
+        C_MEMBER_HI   = 4
+    };
+
+    struct slot_view
+    {
+        float *x, *y, *vx, *vy, *fuel, *cx, *lpad, *lpad_r;
+        int *steps, *layout, *active;
+        double* acc;
+        __device__ __forceinline__ slot_view(unsigned char* base, int S)
+        {
+            acc    = reinterpret_cast<double*>(base);
+            x      = reinterpret_cast<float*>(acc + S);
+            y = x + S, vx = y + S, vy = vx + S, fuel = vy + S, cx = fuel + S, lpad = cx + S, lpad_r = lpad + S;
+            steps  = reinterpret_cast<int*>(lpad_r + S);
+            layout = steps + S, active = layout + S;
+        }
+        static __host__ __device__ int bytes(int S) { return S * (8 + 8 * 4 + 3 * 4); }
+    };
+
+    __device__ __forceinline__ float fast_act(float z, int act) { return ll_ops<float, LL_MODE_FAST>::act(z, act); }
+
+    // One (episode group, output group, k-slice) register tile: acc[e][j] = sum_k in[k][e*Ge + ge] * W[k][go*8 + j]
+    template <int E>
+    __device__ __forceinline__ void gemm_tile(const float* __restrict__ wp, const float* __restrict__ ap, int klen, int out_pad, int S, int Ge,
+                                              float (&acc)[E][FO])
+    {
+#pragma unroll
+        for (int e = 0; e < E; ++e)
+#pragma unroll
+            for (int j = 0; j < FO; ++j) acc[e][j] = 0.f;
+#pragma unroll 4
+        for (int k = 0; k < klen; ++k)
+        {
+            const float4 w0 = *reinterpret_cast<const float4*>(wp + (size_t)k * out_pad);
+            const float4 w1 = *reinterpret_cast<const float4*>(wp + (size_t)k * out_pad + 4);
+            float av[E];
+#pragma unroll
+            for (int e = 0; e < E; ++e) av[e] = ap[k * S + e * Ge];
+#pragma unroll
+            for (int e = 0; e < E; ++e)
+            {
+                acc[e][0] = fmaf(av[e], w0.x, acc[e][0]);
+                acc[e][1] = fmaf(av[e], w0.y, acc[e][1]);
+                acc[e][2] = fmaf(av[e], w0.z, acc[e][2]);
+                acc[e][3] = fmaf(av[e], w0.w, acc[e][3]);
+                acc[e][4] = fmaf(av[e], w1.x, acc[e][4]);
+                acc[e][5] = fmaf(av[e], w1.y, acc[e][5]);
+                acc[e][6] = fmaf(av[e], w1.z, acc[e][6]);
+                acc[e][7] = fmaf(av[e], w1.w, acc[e][7]);
+            }
+        }
+    }
+
+    // One layer for one team.  Layers with ks == 1 (and not the output layer) write activations directly; the others
+    // leave partial sums part[(slice * out_pad + o) * S + slot], reduced by layer_reduce (hidden layers) or by the
+    // env phase (output layer).
+    template <int E>
+    __device__ __forceinline__ void layer_gemm(const fast_args& a, const fast_layer& ly, const float* __restrict__ W, float* __restrict__ ACT,
+                                               int tt)
+    {
+        const int S = a.S, Ge = a.Ge;
+        const float* in = ACT + ly.in_off;
+        const int work  = ly.tiles * ly.ks;
+        for (int idx = tt; idx < work; idx += a.TS)
+        {
+            const int ks = idx / ly.tiles, tile = idx - ks * ly.tiles;
+            const int go = tile / Ge, ge = tile - go * Ge;
+            const int k0 = ks * ly.klen;
+            const int kl = min(ly.klen, ly.in - k0);
+            float acc[E][FO];
+            gemm_tile<E>(W + ly.w_off + (size_t)k0 * ly.out_pad + go * FO, in + k0 * S + ge, kl, ly.out_pad, S, Ge, acc);
+            if (ly.ks == 1 && !ly.last)
+            {
+                float* out       = ACT + ly.out_off;
+                const float* b   = W + ly.b_off + go * FO;
+                const float4 b0 = *reinterpret_cast<const float4*>(b), b1 = *reinterpret_cast<const float4*>(b + 4);
+                const float bv[FO] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+                for (int j = 0; j < FO; ++j)
+                    if (go * FO + j < ly.out)
+                    {
+#pragma unroll
+                        for (int e = 0; e < E; ++e) out[(go * FO + j) * S + e * Ge + ge] = fast_act(acc[e][j] + bv[j], a.act);
+                    }
+            }
+            else
+            {
+                float* part = ACT + a.part_off + (size_t)ks * ly.out_pad * S;
+#pragma unroll
+                for (int j = 0; j < FO; ++j)
+                    if (go * FO + j < ly.out)
+                    {
+#pragma unroll
+                        for (int e = 0; e < E; ++e) part[(go * FO + j) * S + e * Ge + ge] = acc[e][j];
+                    }
+            }
+        }
+    }
+
+    __device__ __forceinline__ void layer_reduce(const fast_args& a, const fast_layer& ly, const float* __restrict__ W, float* __restrict__ ACT, int tt)
+    {
+        const int S       = a.S;
+        const float* part = ACT + a.part_off;
+        float* out        = ACT + ly.out_off;
+        const int n       = ly.out * S;
+        for (int i = tt; i < n; i += a.TS)
+        {
+            const int o = i / S;
+            float v     = W[ly.b_off + o];
+            for (int s = 0; s < ly.ks; ++s) v += part[(size_t)s * ly.out_pad * S + i];
+            out[i] = fast_act(v, a.act);
+        }
+    }
+
+    // begin an episode of layout l in slot s (reset(spad_x1, lpad_x1), src/game_logic.cpp:143-154) and publish its state
+    __device__ __forceinline__ void slot_begin(const fast_args& a, const ll_env<float>& env, slot_view& sv, float* A0, int s, int l)
+    {
+        const ll_layout<float> lay = a.layouts[l];
+        sv.layout[s] = l | (lay.dir << 30);
+        sv.cx[s] = lay.center_x, sv.lpad[s] = lay.lpad_x1, sv.lpad_r[s] = lay.lpad_right;
+        ll_lander<float> p{lay.init_x, env.y0, env.vx0, env.vy0, env.max_fuel};
+        sv.x[s] = p.x, sv.y[s] = p.y, sv.vx[s] = p.vx, sv.vy[s] = p.vy, sv.fuel[s] = p.fuel;
+        sv.steps[s] = 0, sv.acc[s] = 0.0, sv.active[s] = 1;
+        ll_get_state<float, LL_MODE_FAST>(env, p, lay.center_x, A0 + s, a.S);
+    }
+
+    // env phase of one active slot: output layer reduce -> argmax -> update -> penalties -> next state / next layout
+    __device__ __forceinline__ void slot_step(const fast_args& a, const ll_env<float>& env, slot_view& sv, const float* __restrict__ W,
+                                              float* __restrict__ ACT, int* ctl, double* res_fit, int* res_meta, unsigned long long member, int s)
+    {
+        const fast_layer& ly = a.layer[a.n_layers - 1];
+        const float* part    = ACT + a.part_off;
+        int action = 0;
+        float vbest = 0.f;
+        for (int o = 0; o < ly.out; ++o)
+        {
+            float v = W[ly.b_off + o];
+            for (int k = 0; k < ly.ks; ++k) v += part[((size_t)k * ly.out_pad + o) * a.S + s];
+            v = fast_act(v, a.act);
+            if (o == 0 || v > vbest) vbest = v, action = o;
+        }
+        ll_lander<float> p{sv.x[s], sv.y[s], sv.vx[s], sv.vy[s], sv.fuel[s]};
+        const float cx = sv.cx[s];
+        int steps      = sv.steps[s];
+        bool landed, success;
+        float dist;
+        const float sp = ll_env_step<float, LL_MODE_FAST>(env, p, action, steps == 0, cx, sv.lpad[s], sv.lpad_r[s], &landed, &success, &dist);
+        const double acc = sv.acc[s] + (double)sp;
+        ++steps;
+        float* A0 = ACT + a.layer[0].in_off;
+        if (landed || steps >= a.max_steps)
+        {
+            const float term = ll_terminal_penalty<float, LL_MODE_FAST>(env, p, steps, landed, success, dist);
+            const double fit = (double)term + acc;
+            const int lw     = sv.layout[s];
+            const int layout = lw & 0x3fffffff;
+            const int meta   = steps | (landed ? (1 << 28) : 0) | ((landed && !success) ? (1 << 29) : 0) | (success ? (1 << 30) : 0);
+            if (a.res_in_smem) res_fit[layout] = fit, res_meta[layout] = meta;
+            if (a.ep_steps)
+            {
+                a.ep_steps[member * (size_t)a.n_layouts + layout] = meta;
+                a.ep_fit[member * (size_t)a.n_layouts + layout]   = fit;
+            }
+            const int nl = atomicAdd(&ctl[C_NEXT_LAYOUT], 1);
+            if (nl < a.n_layouts) slot_begin(a, env, sv, A0, s, nl);
+            else
+            {
+                sv.active[s] = 0;
+                atomicSub(&ctl[C_N_ACTIVE], 1);
+            }
+            return;
+        }
+        sv.x[s] = p.x, sv.y[s] = p.y, sv.vx[s] = p.vx, sv.vy[s] = p.vy, sv.fuel[s] = p.fuel;
+        sv.steps[s] = steps, sv.acc[s] = acc;
+        ll_get_state<float, LL_MODE_FAST>(env, p, cx, A0 + s, a.S);
+    }
+
+    // per-member totals in layout order (src/nn_engine_trainer.cpp:518-530), by the team leader
+    __device__ void member_finalize(const fast_args& a, const ll_env<float>& env, const double* res_fit, const int* res_meta,
+                                    unsigned long long member)
+    {
+        double total = 0.0, total_steps = 0.0;
+        float bonus0 = 0.f, bonus1 = 0.f;
+        for (int l = 0; l < a.n_layouts; ++l)
+        {
+            const int meta   = a.res_in_smem ? res_meta[l] : a.ep_steps[member * (size_t)a.n_layouts + l];
+            const double fit = a.res_in_smem ? res_fit[l] : a.ep_fit[member * (size_t)a.n_layouts + l];
+            total += fit;
+            total_steps += (double)(meta & 0x0fffffff);
+            if (meta & (1 << 30))
+            {
+                if (a.layouts[l].dir == 0) bonus0 += env.tp_landed_lr_bonus;
+                else bonus1 += env.tp_landed_lr_bonus;
+            }
+        }
+        const double lr = (double)(bonus1 < bonus0 ? bonus1 : bonus0);
+        a.fitness[member] = total - lr;
+        a.lr[member]      = lr;
+        a.steps[member]   = total_steps;
+    }
+
+    template <int E>
+    __global__ void __launch_bounds__(MAX_THREADS) ll_episode_fast_kernel(const __grid_constant__ ll_env<float> env, const __grid_constant__ fast_args a)
+    {
+        extern __shared__ __align__(128) unsigned char smem_raw[];
+        const int tid = threadIdx.x, team = tid / a.TS, tt = tid - team * a.TS;
+        const bool in_team = team < a.NT; // threads past the last whole team only take part in the barriers
+        unsigned char* tb  = smem_raw + (size_t)(in_team ? team : 0) * a.team_bytes;
+        uint64_t* bar      = reinterpret_cast<uint64_t*>(tb);
+        int* ctl           = reinterpret_cast<int*>(tb + 16);
+        float* W           = reinterpret_cast<float*>(tb + a.off_w);
+        float* ACT         = reinterpret_cast<float*>(tb + a.off_act);
+        slot_view sv(tb + a.off_slot, a.S);
+        double* res_fit = reinterpret_cast<double*>(tb + a.off_res);
+        int* res_meta   = reinterpret_cast<int*>(res_fit + (a.res_in_smem ? a.n_layouts : 0));
+        const uint32_t row_bytes = (uint32_t)a.p_dev * sizeof(float);
+
+        if (in_team && tt == 0)
+        {
+            ll_mbar_init(bar, 1);
+            ctl[C_N_ACTIVE] = 0, ctl[C_HAS_MEMBER] = 0, ctl[C_NEXT_LAYOUT] = 0;
+        }
+        __syncthreads();
+        uint32_t phase            = 0;
+        bool running              = false;  // the team holds a member whose episodes are in flight
+        bool finished             = !in_team; // the queue is exhausted for this team
+        unsigned long long member = 0;
+
+        for (;;)
+        {
+            // ---- env phase: one thread per slot
+            if (running)
+                for (int s = tt; s < a.S; s += a.TS)
+                    if (sv.active[s]) slot_step(a, env, sv, W, ACT, ctl, res_fit, res_meta, member, s);
+            __syncthreads();
+            const bool need = !finished && (!running || ctl[C_N_ACTIVE] == 0);
+            if (__syncthreads_or(need))
+            {
+                // ---- member management (rare): finalize, pull the next member, stage its row with one TMA bulk copy
+                if (need && tt == 0)
+                {
+                    if (running) member_finalize(a, env, res_fit, res_meta, member);
+                    const unsigned long long m = (unsigned long long)atomicAdd(a.queue, 1u);
+                    if (m < a.n_members)
+                    {
+                        ctl[C_HAS_MEMBER] = 1, ctl[C_MEMBER_LO] = (int)(unsigned int)m, ctl[C_MEMBER_HI] = (int)(unsigned int)(m >> 32);
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                        ll_mbar_expect_tx(bar, row_bytes);
+                        ll_bulk_g2s(W, a.params + m * (size_t)a.p_dev, row_bytes, bar);
+                    }
+                    else ctl[C_HAS_MEMBER] = 0;
+                }
+                __syncthreads();
+                if (need)
+                {
+                    if (ctl[C_HAS_MEMBER])
+                    {
+                        member  = (unsigned long long)(unsigned int)ctl[C_MEMBER_LO] | ((unsigned long long)(unsigned int)ctl[C_MEMBER_HI] << 32);
+                        running = true;
+                        ll_mbar_wait(bar, phase);
+                        phase ^= 1u;
+                    }
+                    else running = false, finished = true;
+                }
+                __syncthreads(); // every thread of the team has read the control words before the leader rewrites them
+                if (need && running)
+                {
+                    float* A0 = ACT + a.layer[0].in_off;
+                    for (int s = tt; s < a.S; s += a.TS)
+                    {
+                        if (s < a.n_layouts) slot_begin(a, env, sv, A0, s, s);
+                        else
+                        {
+                            sv.active[s] = 0;
+                            for (int i = 0; i < a.layer[0].in; ++i) A0[i * a.S + s] = 0.f;
+                        }
+                    }
+                    if (tt == 0) ctl[C_NEXT_LAYOUT] = min(a.S, a.n_layouts), ctl[C_N_ACTIVE] = min(a.S, a.n_layouts);
+                }
+                if (__syncthreads_and(finished)) break;
+            }
+            // ---- forward pass: one phase per layer (+ a reduce phase for split-K hidden layers)
+            for (int l = 0; l < a.n_layers; ++l)
+            {
+                const fast_layer& ly = a.layer[l];
+                if (running) layer_gemm<E>(a, ly, W, ACT, tt);
+                __syncthreads();
+                if (ly.ks > 1 && !ly.last)
+                {
+                    if (running) layer_reduce(a, ly, W, ACT, tt);
+                    __syncthreads();
+                }
+            }
+        }
+    }
+
+    int pick_E(int L)
+    { // episode slots per thread: the candidate with the best slot utilisation, larger tiles on ties
+        const int cand[5] = {8, 5, 4, 2, 1};
+        int best = 1;
+        double best_u = -1.0;
+        for (int E : cand)
+        {
+            int Ge = (L + E - 1) / E;
+            if (E * Ge > 64) Ge = 64 / E;
+            const int S = E * Ge, rounds = (L + S - 1) / S;
+            const double u = (double)L / ((double)rounds * S);
+            if (u > best_u + 1e-9) best_u = u, best = E;
+        }
+        return best;
+    }
+
+    template <int E> int launch_fast_t(ll_ctx* ctx, const ll_episode_args& h)
+    {
+        const ll_topo& tp = ctx->topo;
+        fast_args a{};
+        a.params = static_cast<const float*>(h.params), a.layouts = static_cast<const ll_layout<float>*>(h.layouts);
+        a.n_layouts = h.n_layouts, a.max_steps = h.max_steps, a.n_members = h.n_members;
+        a.fitness = h.fitness, a.lr = h.lr, a.steps = h.steps, a.ep_steps = h.ep_steps, a.ep_fit = h.ep_fit, a.queue = h.queue;
+        a.n_layers = tp.n_layers, a.act = tp.activation, a.p_dev = tp.p_dev;
+        const int L = h.n_layouts;
+        int Ge      = (L + E - 1) / E;
+        if (E * Ge > 64) Ge = 64 / E;
+        a.Ge = Ge, a.S = E * Ge;
+        a.res_in_smem = L <= MAX_RES ? 1 : 0;
+        if (!a.res_in_smem && !h.ep_steps) return ll_fail(ctx, LL_EINVAL, "fast episode kernel: more than 256 layouts need the per-episode buffers");
+
+        int nog_max = 1;
+        for (int l = 0; l < tp.n_layers; ++l) nog_max = std::max(nog_max, tp.out_pad[l] / FO);
+        int TS = Ge * nog_max;
+        if (TS > MAX_THREADS) TS = MAX_THREADS;
+        TS   = TS >= 32 ? ((TS + 31) & ~31) : (TS <= 8 ? 8 : (TS <= 16 ? 16 : 32));
+        if (TS > MAX_THREADS) TS = MAX_THREADS;
+        a.TS = TS;
+
+        // activation buffers: even / odd ping-pong sized by the widest activation of each parity, then split-K partials
+        int even = 0, odd = 0, part = 0;
+        for (int l = 0; l <= tp.n_layers; ++l)
+        {
+            const int width = l == 0 ? tp.in[0] : tp.out[l - 1];
+            if (l == tp.n_layers) break; // the output layer only produces partial sums
+            ((l & 1) ? odd : even) = std::max((l & 1) ? odd : even, width * a.S);
+        }
+        for (int l = 0; l < tp.n_layers; ++l)
+        {
+            fast_layer& ly = a.layer[l];
+            ly.in = tp.in[l], ly.out = tp.out[l], ly.out_pad = tp.out_pad[l], ly.w_off = tp.w_off[l], ly.b_off = tp.b_off[l];
+            ly.last  = l == tp.n_layers - 1;
+            ly.nog   = tp.out_pad[l] / FO;
+            ly.tiles = Ge * ly.nog;
+            int ks   = 1;
+            while (ly.tiles * ks * 2 <= TS && ly.in / (ks * 2) >= 8) ks *= 2;
+            ly.ks    = ks;
+            ly.klen  = (ly.in + ks - 1) / ks;
+            ly.in_off  = (l & 1) ? even : 0;
+            ly.out_off = (l & 1) ? 0 : even;
+            if (ks > 1 || ly.last) part = std::max(part, ks * ly.out_pad * a.S);
+        }
+        a.part_off = even + odd;
+        const int act_elems = even + odd + part;
+        auto up             = [](int v) { return (v + 127) & ~127; };
+        a.off_w             = 128;
+        a.off_act           = up(a.off_w + tp.p_dev * 4);
+        a.off_slot          = up(a.off_act + act_elems * 4);
+        a.off_res           = up(a.off_slot + slot_view::bytes(a.S));
+        a.team_bytes        = up(a.off_res + (a.res_in_smem ? L * 12 : 0) + 16);
+
+        int max_smem = 0;
+        LL_CUDA(ctx, cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device));
+        if (a.team_bytes > max_smem) return ll_fail(ctx, LL_EINVAL, "fast episode kernel: a member team needs " + std::to_string(a.team_bytes) + " B of shared memory");
+        // teams per CTA: fill up to 256 threads, but keep at least two CTAs per SM when the topology allows it
+        int NT = std::max(1, MAX_THREADS / TS);
+        while (NT > 1 && (size_t)NT * a.team_bytes > (size_t)max_smem / 2) --NT;
+        const unsigned long long teams_needed = h.n_members;
+        if ((unsigned long long)NT > teams_needed) NT = (int)teams_needed;
+        a.NT              = NT;
+        const int threads = NT * TS;
+        const size_t smem = (size_t)NT * a.team_bytes;
+        auto kern         = ll_episode_fast_kernel<E>;
+        LL_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int per_sm = 0;
+        LL_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
+        if (per_sm < 1) return ll_fail(ctx, LL_EINVAL, "fast episode kernel does not fit on an SM");
+        unsigned long long blocks_needed = (h.n_members + NT - 1) / NT;
+        unsigned int grid                = (unsigned int)std::min<unsigned long long>((unsigned long long)per_sm * ctx->sm_count, blocks_needed);
+        if (grid < 1) grid = 1;
+        ll_env<float> env;
+        ll_make_env<float>(ctx->env_cfg, 1, &env);
+        LL_CUDA(ctx, cudaMemsetAsync(h.queue, 0, sizeof(unsigned int), ctx->stream));
+        kern<<<grid, threads, smem, ctx->stream>>>(env, a);
+        LL_CUDA(ctx, cudaGetLastError());
+        return LL_OK;
+    }
+} // namespace
+
+// Fast-mode launcher; returns LL_OK after enqueueing, or a negative value when the team kernel does not apply
+// (single-layout evaluations and traces stay on the lane-per-episode kernel of ll_episode.cu).
+int ll_launch_episode_fast(ll_ctx* ctx, const ll_episode_args& a)
+{
+    switch (pick_E(a.n_layouts))
+    {
+    case 8: return launch_fast_t<8>(ctx, a);
+    case 5: return launch_fast_t<5>(ctx, a);
+    case 4: return launch_fast_t<4>(ctx, a);
+    case 2: return launch_fast_t<2>(ctx, a);
+    default: return launch_fast_t<1>(ctx, a);
+    }
+}

@@ -17,7 +17,7 @@ void ll_build_topo(const std::vector<uint64_t>& sizes, int activation, ll_topo* 
     int canon = 0, dev = 0;
     for (int l = 0; l < t->n_layers; ++l)
     {
-        const int in = (int)sizes[l], out = (int)sizes[l + 1], op = (out + 3) & ~3;
+        const int in = (int)sizes[l], out = (int)sizes[l + 1], op = (out + 7) & ~7;
         t->in[l] = in, t->out[l] = out, t->out_pad[l] = op;
         t->w_off[l] = dev;
         t->b_off[l] = dev + in * op;

@@ -18,8 +18,9 @@
 // Network topology in the device ("forward") layout.  A member row holds, for each layer l:
 //   Wt_l[k][out_pad_l]  k = 0..in_l-1   (k-major = transposed w.r.t. the weight file's [out][in]; pad columns are 0)
 //   b_l[out_pad_l]
-// out_pad_l = out_l rounded up to a multiple of 4, so every k-row starts on a 16-byte boundary for
-// both float (LDS.128 = 4 outputs) and double (LDS.128 = 2 outputs).
+// out_pad_l = out_l rounded up to a multiple of 8, so every k-row starts on a 32-byte boundary: two LDS.128 fetch
+// the 8 consecutive outputs of a register tile in the fast kernel (float), and every tile width of the exact
+// kernel (16 / 8 / 4 outputs) divides a row.
 struct ll_topo
 {
     int n_layers;
@@ -148,6 +149,7 @@ struct ll_episode_args
     ll_episode_result* trace_result;
 };
 int ll_launch_episode(ll_ctx* ctx, const ll_episode_args& a);
+int ll_launch_episode_fast(ll_ctx* ctx, const ll_episode_args& a); // ll_episode_fast.cu
 int ll_launch_feedforward(ll_ctx* ctx, const void* member_row, const void* d_state, unsigned long long* d_action);
 const char* ll_episode_kernel_name(const ll_ctx* ctx, int n_layouts);
 

@@ -123,6 +123,7 @@ class Engine:
         d = np.ascontiguousarray(directions, dtype=np.uint64)
         check(lib.ll_set_layouts(self._h, _p(s, C.c_int32), _p(l, C.c_int32), _p(d, C.c_uint64), len(s)), self._h)
         self.n_layouts = len(s)
+        check(lib.ll_get_info(self._h, C.byref(self.info)), self._h)  # the episode-kernel variant depends on the layout count
 
     def evaluate_device(self, max_steps: int):
         check(lib.ll_evaluate_device(self._h, max_steps), self._h)
@@ -146,6 +147,7 @@ class Engine:
         check(lib.ll_evaluate(self._h, _p(s, C.c_int32), _p(l, C.c_int32), _p(d, C.c_uint64), len(s), max_steps,
                               _p(f[0], C.c_double), _p(f[1], C.c_double), _p(f[2], C.c_double), C.byref(st)), self._h)
         self.n_layouts = len(s)
+        check(lib.ll_get_info(self._h, C.byref(self.info)), self._h)
         return f[0], f[1], f[2], st
 
     def read_episodes(self):

@@ -303,20 +303,50 @@ def test_weight_file_roundtrip(ll, po, tmp_path):
 
 
 # 7. fast fp32 mode: judged on outcomes, not sequences
-def test_fast_mode_outcomes(ll, po):
-    topo = "16_64_32"
-    members, sizes = util.elite_population(topo, 256, 4, noise=0.02)
+@pytest.mark.parametrize("topo,n_layouts,pop", [("16_64_32", 50, 256), ("32_128_32", 50, 96), ("16_64_32", 8, 512), ("8_16_8", 33, 300),
+                                                ("16_16", 5, 777), ("8_16_32_16_8", 50, 64), ("16_16", 1, 2048)])
+def test_fast_mode_outcomes(ll, po, topo, n_layouts, pop):
+    """LL_MODE_FAST (team-GEMM kernel for >= 4 layouts, lane-per-episode kernel below): FMA, free summation order and
+    tanh.approx.f32 change individual trajectories, so the bar is statistical — stated here: landed-successfully rate
+    within 2 points, total lander steps within 2 %, mean fitness within 3 % of the mean |fitness| of the exact fp32 path."""
+    members, sizes = util.elite_population(topo, pop, 4, noise=0.02)
+    members[pop // 2:] += util.random_population(sizes, pop - pop // 2, 8, scale=0.05)  # a more diverse half
     spad, lpad, d = util.layouts(50)
-    eng, cfg = _engine(ll, sizes, 256, 32, mode=1)
+    spad, lpad, d = spad[:n_layouts], lpad[:n_layouts], d[:n_layouts]
+    eng, cfg = _engine(ll, sizes, pop, 32, mode=1)
     eng.set_members(0, members)
     fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
-    _, flags, _ = eng.read_episodes()
+    ep_steps, flags, ep_fit = eng.read_episodes()
     want = po.evaluate(cfg.env_cfg(), sizes, 1, members.astype(np.float32), spad, lpad, d, 5000, 32, threads=8)
+    assert np.array_equal(steps, ep_steps.sum(axis=1).astype(np.float64))
+    assert st.sum_steps == steps.sum() and st.members == pop
     rate_gpu, rate_cpu = (flags & 4).astype(bool).mean(), (want["ep_flags"] & 4).astype(bool).mean()
-    assert abs(rate_gpu - rate_cpu) <= 0.02, (rate_gpu, rate_cpu)                       # landed-successfully rate within 2 points
-    assert abs(steps.sum() - want["steps"].sum()) <= 0.02 * want["steps"].sum()         # total steps within 2 %
+    assert abs(rate_gpu - rate_cpu) <= 0.02, (rate_gpu, rate_cpu)
+    assert abs(steps.sum() - want["steps"].sum()) <= 0.02 * want["steps"].sum(), (steps.sum(), want["steps"].sum())
     scale = np.abs(want["fitness"]).mean()
-    assert abs(fit.mean() - want["fitness"].mean()) <= 0.03 * scale                     # mean fitness within 3 % of its magnitude
+    assert abs(fit.mean() - want["fitness"].mean()) <= 0.03 * scale, (fit.mean(), want["fitness"].mean())
+    # most members behave identically: the median per-member step difference is tiny
+    assert np.median(np.abs(steps - want["steps"]) / want["steps"]) <= 0.01
+    eng.close()
+
+
+def test_fast_mode_constant_policies(ll):
+    """Constant-action networks do not depend on the forward arithmetic: the fast kernel must reproduce the reference-owned
+    known answers of the environment in step counts and flags, fitness to float rounding."""
+    sizes = [5, 16, 16, 4]
+    eng, cfg = _engine(ll, sizes, 4, 32, mode=1)
+    for a in range(4):
+        eng.set_members(a, util.constant_action_member(sizes, a)[None, :])
+    known = [g for g in util.golden()["env_known_answers"] if g["precision"] == 32]
+    spad, lpad, d = util.layouts(8)
+    spad[0], lpad[0], d[0] = known[0]["spad_x1"], known[0]["lpad_x1"], 0
+    fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
+    ep_steps, flags, ep_fit = eng.read_episodes()
+    for g in known:
+        a = g["action"]
+        assert ep_steps[a, 0] == g["steps"] and flags[a, 0] == g["flags"]
+        want = g["step_penalty_sum"] + g["terminal_penalty"]
+        assert abs(ep_fit[a, 0] - want) <= 2e-4 * abs(want)
     eng.close()
 
 
