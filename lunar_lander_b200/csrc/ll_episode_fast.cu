@@ -54,7 +54,8 @@ namespace
         C_N_ACTIVE    = 1,
         C_HAS_MEMBER  = 2,
         C_MEMBER_LO   = 3,
-        C_MEMBER_HI   = 4
+        C_MEMBER_HI   = 4,
+        C_DIRTY       = 5
     };
 
     struct slot_view
@@ -75,9 +76,10 @@ namespace
 
     __device__ __forceinline__ float fast_act(float z, int act) { return ll_ops<float, LL_MODE_FAST>::act(z, act); }
 
-    // One (episode group, output group, k-slice) register tile: acc[e][j] = sum_k in[k][e*Ge + ge] * W[k][go*8 + j]
+    // One (episode group, output group, k-slice) register tile: acc[e][j] = sum_k in[k][ge*E + e] * W[k][go*8 + j].
+    // Pointer-increment form: per k two row-pointer bumps, two LDS.128 (weights), E LDS.32 (activations), E*8 FFMA.
     template <int E>
-    __device__ __forceinline__ void gemm_tile(const float* __restrict__ wp, const float* __restrict__ ap, int klen, int out_pad, int S, int Ge,
+    __device__ __forceinline__ void gemm_tile(const float* __restrict__ wp, const float* __restrict__ ap, int klen, int out_pad, int S,
                                               float (&acc)[E][FO])
     {
 #pragma unroll
@@ -87,11 +89,12 @@ namespace
 #pragma unroll 4
         for (int k = 0; k < klen; ++k)
         {
-            const float4 w0 = *reinterpret_cast<const float4*>(wp + (size_t)k * out_pad);
-            const float4 w1 = *reinterpret_cast<const float4*>(wp + (size_t)k * out_pad + 4);
+            const float4 w0 = *reinterpret_cast<const float4*>(wp);
+            const float4 w1 = *reinterpret_cast<const float4*>(wp + 4);
             float av[E];
 #pragma unroll
-            for (int e = 0; e < E; ++e) av[e] = ap[k * S + e * Ge];
+            for (int e = 0; e < E; ++e) av[e] = ap[e];
+            wp += out_pad, ap += S;
 #pragma unroll
             for (int e = 0; e < E; ++e)
             {
@@ -107,12 +110,13 @@ namespace
         }
     }
 
-    // One layer for one team.  Layers with ks == 1 (and not the output layer) write activations directly; the others
-    // leave partial sums part[(slice * out_pad + o) * S + slot], reduced by layer_reduce (hidden layers) or by the
-    // env phase (output layer).
+    // One layer for one team.  Slots are kept compacted (active slots are [0, n_act)), and a thread's E slots are
+    // contiguous (slot = ge*E + e), so tiles of episode groups past n_act are skipped.  Layers with ks == 1 (and not the
+    // output layer) write activations directly; the others leave partial sums part[(slice * out_pad + o) * S + slot],
+    // reduced by layer_reduce (hidden layers) or by the env phase (output layer).
     template <int E>
     __device__ __forceinline__ void layer_gemm(const fast_args& a, const fast_layer& ly, const float* __restrict__ W, float* __restrict__ ACT,
-                                               int tt)
+                                               int tt, int n_act)
     {
         const int S = a.S, Ge = a.Ge;
         const float* in = ACT + ly.in_off;
@@ -121,14 +125,15 @@ namespace
         {
             const int ks = idx / ly.tiles, tile = idx - ks * ly.tiles;
             const int go = tile / Ge, ge = tile - go * Ge;
+            if (ge * E >= n_act) continue;
             const int k0 = ks * ly.klen;
             const int kl = min(ly.klen, ly.in - k0);
             float acc[E][FO];
-            gemm_tile<E>(W + ly.w_off + (size_t)k0 * ly.out_pad + go * FO, in + k0 * S + ge, kl, ly.out_pad, S, Ge, acc);
+            gemm_tile<E>(W + ly.w_off + k0 * ly.out_pad + go * FO, in + k0 * S + ge * E, kl, ly.out_pad, S, acc);
             if (ly.ks == 1 && !ly.last)
             {
-                float* out       = ACT + ly.out_off;
-                const float* b   = W + ly.b_off + go * FO;
+                float* out      = ACT + ly.out_off + (go * FO) * S + ge * E;
+                const float* b  = W + ly.b_off + go * FO;
                 const float4 b0 = *reinterpret_cast<const float4*>(b), b1 = *reinterpret_cast<const float4*>(b + 4);
                 const float bv[FO] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
@@ -136,35 +141,36 @@ namespace
                     if (go * FO + j < ly.out)
                     {
 #pragma unroll
-                        for (int e = 0; e < E; ++e) out[(go * FO + j) * S + e * Ge + ge] = fast_act(acc[e][j] + bv[j], a.act);
+                        for (int e = 0; e < E; ++e) out[j * S + e] = fast_act(acc[e][j] + bv[j], a.act);
                     }
             }
             else
             {
-                float* part = ACT + a.part_off + (size_t)ks * ly.out_pad * S;
+                float* part = ACT + a.part_off + (ks * ly.out_pad + go * FO) * S + ge * E;
 #pragma unroll
                 for (int j = 0; j < FO; ++j)
                     if (go * FO + j < ly.out)
                     {
 #pragma unroll
-                        for (int e = 0; e < E; ++e) part[(go * FO + j) * S + e * Ge + ge] = acc[e][j];
+                        for (int e = 0; e < E; ++e) part[j * S + e] = acc[e][j];
                     }
             }
         }
     }
 
-    __device__ __forceinline__ void layer_reduce(const fast_args& a, const fast_layer& ly, const float* __restrict__ W, float* __restrict__ ACT, int tt)
+    __device__ __forceinline__ void layer_reduce(const fast_args& a, const fast_layer& ly, const float* __restrict__ W, float* __restrict__ ACT, int tt,
+                                                 int n_act)
     {
         const int S       = a.S;
         const float* part = ACT + a.part_off;
         float* out        = ACT + ly.out_off;
-        const int n       = ly.out * S;
+        const int n       = ly.out * n_act;
         for (int i = tt; i < n; i += a.TS)
         {
-            const int o = i / S;
+            const int o = i / n_act, s = i - o * n_act;
             float v     = W[ly.b_off + o];
-            for (int s = 0; s < ly.ks; ++s) v += part[(size_t)s * ly.out_pad * S + i];
-            out[i] = fast_act(v, a.act);
+            for (int q = 0; q < ly.ks; ++q) v += part[(q * ly.out_pad + o) * S + s];
+            out[o * S + s] = fast_act(v, a.act);
         }
     }
 
@@ -222,13 +228,34 @@ namespace
             else
             {
                 sv.active[s] = 0;
-                atomicSub(&ctl[C_N_ACTIVE], 1);
+                ctl[C_DIRTY] = 1; // compacted by the team leader before the next forward pass
             }
             return;
         }
         sv.x[s] = p.x, sv.y[s] = p.y, sv.vx[s] = p.vx, sv.vy[s] = p.vy, sv.fuel[s] = p.fuel;
         sv.steps[s] = steps, sv.acc[s] = acc;
         ll_get_state<float, LL_MODE_FAST>(env, p, cx, A0 + s, a.S);
+    }
+
+    // Keep the active slots packed in [0, n_act): holes left by finished episodes are filled from the top.  Rare (at most
+    // once per finished episode), done serially by the team leader; the moved slot's input column is rebuilt.
+    __device__ void team_compact(const fast_args& a, const ll_env<float>& env, slot_view& sv, float* A0, int* ctl)
+    {
+        int i = 0, j = ctl[C_N_ACTIVE] - 1;
+        for (;;)
+        {
+            while (i <= j && sv.active[i]) ++i;
+            while (j >= i && !sv.active[j]) --j;
+            if (i >= j) break;
+            sv.acc[i] = sv.acc[j];
+            sv.x[i] = sv.x[j], sv.y[i] = sv.y[j], sv.vx[i] = sv.vx[j], sv.vy[i] = sv.vy[j], sv.fuel[i] = sv.fuel[j];
+            sv.cx[i] = sv.cx[j], sv.lpad[i] = sv.lpad[j], sv.lpad_r[i] = sv.lpad_r[j];
+            sv.steps[i] = sv.steps[j], sv.layout[i] = sv.layout[j];
+            sv.active[i] = 1, sv.active[j] = 0;
+            for (int q = 0; q < a.layer[0].in; ++q) A0[q * a.S + i] = A0[q * a.S + j];
+        }
+        ctl[C_N_ACTIVE] = j + 1; // j is the last active slot (or -1)
+        ctl[C_DIRTY]    = 0;
     }
 
     // per-member totals in layout order (src/nn_engine_trainer.cpp:518-530), by the team leader
@@ -259,40 +286,47 @@ namespace
     __global__ void __launch_bounds__(MAX_THREADS) ll_episode_fast_kernel(const __grid_constant__ ll_env<float> env, const __grid_constant__ fast_args a)
     {
         extern __shared__ __align__(128) unsigned char smem_raw[];
+        __shared__ fast_layer s_layer[LL_MAX_LAYERS]; // the layer table in shared memory: indexed reads of kernel parameters are slow
         const int tid = threadIdx.x, team = tid / a.TS, tt = tid - team * a.TS;
-        const bool in_team = team < a.NT; // threads past the last whole team only take part in the barriers
-        unsigned char* tb  = smem_raw + (size_t)(in_team ? team : 0) * a.team_bytes;
-        uint64_t* bar      = reinterpret_cast<uint64_t*>(tb);
-        int* ctl           = reinterpret_cast<int*>(tb + 16);
-        float* W           = reinterpret_cast<float*>(tb + a.off_w);
-        float* ACT         = reinterpret_cast<float*>(tb + a.off_act);
+        unsigned char* tb = smem_raw + (size_t)team * a.team_bytes;
+        uint64_t* bar     = reinterpret_cast<uint64_t*>(tb);
+        int* ctl          = reinterpret_cast<int*>(tb + 16);
+        float* W          = reinterpret_cast<float*>(tb + a.off_w);
+        float* ACT        = reinterpret_cast<float*>(tb + a.off_act);
         slot_view sv(tb + a.off_slot, a.S);
         double* res_fit = reinterpret_cast<double*>(tb + a.off_res);
         int* res_meta   = reinterpret_cast<int*>(res_fit + (a.res_in_smem ? a.n_layouts : 0));
+        float* A0       = ACT + a.layer[0].in_off;
         const uint32_t row_bytes = (uint32_t)a.p_dev * sizeof(float);
+        const int n_layers       = a.n_layers;
 
-        if (in_team && tt == 0)
+        for (int i = tid; i < n_layers; i += blockDim.x) s_layer[i] = a.layer[i];
+        if (tt == 0)
         {
             ll_mbar_init(bar, 1);
-            ctl[C_N_ACTIVE] = 0, ctl[C_HAS_MEMBER] = 0, ctl[C_NEXT_LAYOUT] = 0;
+            ctl[C_N_ACTIVE] = 0, ctl[C_HAS_MEMBER] = 0, ctl[C_NEXT_LAYOUT] = 0, ctl[C_DIRTY] = 0;
         }
         __syncthreads();
         uint32_t phase            = 0;
-        bool running              = false;  // the team holds a member whose episodes are in flight
-        bool finished             = !in_team; // the queue is exhausted for this team
+        bool running              = false; // the team holds a member whose episodes are in flight
+        bool finished             = false; // the queue is exhausted for this team
         unsigned long long member = 0;
+        int n_act                 = 0;
 
         for (;;)
         {
-            // ---- env phase: one thread per slot
+            // ---- env phase: one thread per active slot
             if (running)
-                for (int s = tt; s < a.S; s += a.TS)
-                    if (sv.active[s]) slot_step(a, env, sv, W, ACT, ctl, res_fit, res_meta, member, s);
+                for (int s = tt; s < n_act; s += a.TS) slot_step(a, env, sv, W, ACT, ctl, res_fit, res_meta, member, s);
             __syncthreads();
-            const bool need = !finished && (!running || ctl[C_N_ACTIVE] == 0);
-            if (__syncthreads_or(need))
+            const bool dirty = running && ctl[C_DIRTY] != 0;
+            if (__syncthreads_or(dirty || (!finished && !running)))
             {
-                // ---- member management (rare): finalize, pull the next member, stage its row with one TMA bulk copy
+                // ---- rare path: compaction after finished episodes; member hand-over when none is left
+                if (dirty && tt == 0) team_compact(a, env, sv, A0, ctl);
+                __syncthreads();
+                if (running) n_act = ctl[C_N_ACTIVE];
+                const bool need = !finished && (!running || n_act == 0);
                 if (need && tt == 0)
                 {
                     if (running) member_finalize(a, env, res_fit, res_meta, member);
@@ -316,34 +350,30 @@ namespace
                         ll_mbar_wait(bar, phase);
                         phase ^= 1u;
                     }
-                    else running = false, finished = true;
+                    else running = false, finished = true, n_act = 0;
                 }
                 __syncthreads(); // every thread of the team has read the control words before the leader rewrites them
                 if (need && running)
                 {
-                    float* A0 = ACT + a.layer[0].in_off;
+                    n_act = min(a.S, a.n_layouts);
                     for (int s = tt; s < a.S; s += a.TS)
                     {
-                        if (s < a.n_layouts) slot_begin(a, env, sv, A0, s, s);
-                        else
-                        {
-                            sv.active[s] = 0;
-                            for (int i = 0; i < a.layer[0].in; ++i) A0[i * a.S + s] = 0.f;
-                        }
+                        if (s < n_act) slot_begin(a, env, sv, A0, s, s);
+                        else sv.active[s] = 0;
                     }
-                    if (tt == 0) ctl[C_NEXT_LAYOUT] = min(a.S, a.n_layouts), ctl[C_N_ACTIVE] = min(a.S, a.n_layouts);
+                    if (tt == 0) ctl[C_NEXT_LAYOUT] = n_act, ctl[C_N_ACTIVE] = n_act, ctl[C_DIRTY] = 0;
                 }
                 if (__syncthreads_and(finished)) break;
             }
             // ---- forward pass: one phase per layer (+ a reduce phase for split-K hidden layers)
-            for (int l = 0; l < a.n_layers; ++l)
+            for (int l = 0; l < n_layers; ++l)
             {
-                const fast_layer& ly = a.layer[l];
-                if (running) layer_gemm<E>(a, ly, W, ACT, tt);
+                const fast_layer ly = s_layer[l];
+                if (running) layer_gemm<E>(a, ly, W, ACT, tt, n_act);
                 __syncthreads();
                 if (ly.ks > 1 && !ly.last)
                 {
-                    if (running) layer_reduce(a, ly, W, ACT, tt);
+                    if (running) layer_reduce(a, ly, W, ACT, tt, n_act);
                     __syncthreads();
                 }
             }
