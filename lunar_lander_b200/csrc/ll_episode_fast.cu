@@ -26,7 +26,7 @@ namespace
         int in, out, out_pad, w_off, b_off; // topology (element offsets inside a member row)
         int nog, tiles, ks, klen;           // output groups, (episode group x output group) tiles, k-slices, k per slice
         int in_off, out_off;                // element offsets of the activation buffers inside the team's region
-        int last;                           // output layer: always leaves pre-activation partial sums for the env phase
+        int last;                           // output layer: its activations go to the Z buffer of the env phase
     };
 
     struct fast_args
@@ -41,7 +41,6 @@ namespace
         unsigned int* queue;
         int n_layers, act, p_dev;
         int TS, NT, Ge, S;                                     // threads per team, teams per CTA, episode groups, slots = E * Ge
-        int part_off;                                          // element offset of the split-K partial buffer
         int off_w, off_act, off_slot, off_res, team_bytes;     // byte offsets inside a team's shared-memory region
         int res_in_smem;
         fast_layer layer[LL_MAX_LAYERS];
@@ -110,68 +109,115 @@ namespace
         }
     }
 
-    // One layer for one team.  Slots are kept compacted (active slots are [0, n_act)), and a thread's E slots are
-    // contiguous (slot = ge*E + e), so tiles of episode groups past n_act are skipped.  Layers with ks == 1 (and not the
-    // output layer) write activations directly; the others leave partial sums part[(slice * out_pad + o) * S + slot],
-    // reduced by layer_reduce (hidden layers) or by the env phase (output layer).
-    template <int E>
-    __device__ __forceinline__ void layer_gemm(const fast_args& a, const fast_layer& ly, const float* __restrict__ W, float* __restrict__ ACT,
-                                               int tt, int n_act)
+    // Split-K reduce-scatter inside a warp.  The KS lanes of a tile sit TPW = 32/KS lanes apart (so a quarter-warp reads one
+    // weight row: no bank conflicts); after log2(KS) exchange rounds lane slice `ksi` owns the 8/KS consecutive outputs
+    // starting at j0, fully summed.  res[e][0..8/KS) receives them.
+    template <int E, int KS>
+    __device__ __forceinline__ int reduce_scatter(float (&acc)[E][FO], int ksi, unsigned mask, float (&res)[E][FO / KS])
     {
-        const int S = a.S, Ge = a.Ge;
-        const float* in = ACT + ly.in_off;
-        const int work  = ly.tiles * ly.ks;
-        for (int idx = tt; idx < work; idx += a.TS)
+        constexpr int TPW = 32 / KS;
+        if constexpr (KS == 1)
         {
-            const int ks = idx / ly.tiles, tile = idx - ks * ly.tiles;
-            const int go = tile / Ge, ge = tile - go * Ge;
-            if (ge * E >= n_act) continue;
-            const int k0 = ks * ly.klen;
-            const int kl = min(ly.klen, ly.in - k0);
-            float acc[E][FO];
-            gemm_tile<E>(W + ly.w_off + k0 * ly.out_pad + go * FO, in + k0 * S + ge * E, kl, ly.out_pad, S, acc);
-            if (ly.ks == 1 && !ly.last)
+#pragma unroll
+            for (int e = 0; e < E; ++e)
+#pragma unroll
+                for (int j = 0; j < FO; ++j) res[e][j] = acc[e][j];
+            return 0;
+        }
+        else
+        {
+            const bool b0 = ksi & 1;
+            float r1[E][4];
+#pragma unroll
+            for (int e = 0; e < E; ++e)
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                {
+                    const float send = b0 ? acc[e][j] : acc[e][j + 4];
+                    const float keep = b0 ? acc[e][j + 4] : acc[e][j];
+                    r1[e][j]         = keep + __shfl_xor_sync(mask, send, TPW);
+                }
+            int j0 = b0 ? 4 : 0;
+            if constexpr (KS == 2)
             {
-                float* out      = ACT + ly.out_off + (go * FO) * S + ge * E;
-                const float* b  = W + ly.b_off + go * FO;
-                const float4 b0 = *reinterpret_cast<const float4*>(b), b1 = *reinterpret_cast<const float4*>(b + 4);
-                const float bv[FO] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
-                for (int j = 0; j < FO; ++j)
-                    if (go * FO + j < ly.out)
-                    {
+                for (int e = 0; e < E; ++e)
 #pragma unroll
-                        for (int e = 0; e < E; ++e) out[j * S + e] = fast_act(acc[e][j] + bv[j], a.act);
-                    }
+                    for (int j = 0; j < 4; ++j) res[e][j] = r1[e][j];
+                return j0;
             }
             else
             {
-                float* part = ACT + a.part_off + (ks * ly.out_pad + go * FO) * S + ge * E;
+                const bool b1 = ksi & 2;
 #pragma unroll
-                for (int j = 0; j < FO; ++j)
-                    if (go * FO + j < ly.out)
+                for (int e = 0; e < E; ++e)
+#pragma unroll
+                    for (int j = 0; j < 2; ++j)
                     {
-#pragma unroll
-                        for (int e = 0; e < E; ++e) part[j * S + e] = acc[e][j];
+                        const float send = b1 ? r1[e][j] : r1[e][j + 2];
+                        const float keep = b1 ? r1[e][j + 2] : r1[e][j];
+                        res[e][j]        = keep + __shfl_xor_sync(mask, send, 2 * TPW);
                     }
+                return j0 + (b1 ? 2 : 0);
             }
         }
     }
 
-    __device__ __forceinline__ void layer_reduce(const fast_args& a, const fast_layer& ly, const float* __restrict__ W, float* __restrict__ ACT, int tt,
-                                                 int n_act)
+    // One layer for one team.  Slots are kept compacted (active slots are [0, n_act)) and a thread's E slots are contiguous
+    // (slot = ge*E + e), so tiles of episode groups past n_act are skipped.  KS k-slices of a tile (rows k = KS*i + ksi)
+    // live in one warp and are reduced by shuffles; the owners add the bias, apply the activation and store
+    // out[o][slot].  The output layer stores into the Z buffer the env phase takes its argmax from.
+    template <int E, int KS>
+    __device__ __forceinline__ void layer_phase(const fast_args& a, const fast_layer& ly, const float* __restrict__ W, float* __restrict__ ACT,
+                                                int tt, int n_act)
     {
-        const int S       = a.S;
-        const float* part = ACT + a.part_off;
-        float* out        = ACT + ly.out_off;
-        const int n       = ly.out * n_act;
-        for (int i = tt; i < n; i += a.TS)
+        constexpr int TPW = 32 / KS;
+        const int S = a.S, Ge = a.Ge;
+        const float* in = ACT + ly.in_off;
+        float* outb     = ACT + ly.out_off;
+        int tile, stride, ksi = 0;
+        unsigned mask = 0xffffffffu;
+        if constexpr (KS == 1) tile = tt, stride = a.TS;
+        else
         {
-            const int o = i / n_act, s = i - o * n_act;
-            float v     = W[ly.b_off + o];
-            for (int q = 0; q < ly.ks; ++q) v += part[(q * ly.out_pad + o) * S + s];
-            out[o * S + s] = fast_act(v, a.act);
+            const int lane = tt & 31, q = lane & (TPW - 1);
+            ksi    = lane / TPW;
+            tile   = (tt >> 5) * TPW + q;
+            stride = (a.TS >> 5) * TPW;
+            mask   = 0;
+#pragma unroll
+            for (int i = 0; i < KS; ++i) mask |= 1u << (i * TPW + q);
         }
+        for (; tile < ly.tiles; tile += stride)
+        {
+            const int go = tile / Ge, ge = tile - go * Ge;
+            if (ge * E >= n_act) continue;
+            const int kl = (ly.in - ksi + KS - 1) / KS;
+            float acc[E][FO];
+            gemm_tile<E>(W + ly.w_off + ksi * ly.out_pad + go * FO, in + ksi * S + ge * E, kl, KS * ly.out_pad, KS * S, acc);
+            float res[E][FO / KS];
+            const int j0   = reduce_scatter<E, KS>(acc, ksi, mask, res);
+            const int o0   = go * FO + j0;
+            const float* b = W + ly.b_off + o0;
+            float* out     = outb + o0 * S + ge * E;
+#pragma unroll
+            for (int j = 0; j < FO / KS; ++j)
+                if (o0 + j < ly.out)
+                {
+                    const float bj = b[j];
+#pragma unroll
+                    for (int e = 0; e < E; ++e) out[j * S + e] = fast_act(res[e][j] + bj, a.act);
+                }
+        }
+    }
+
+    template <int E>
+    __device__ __forceinline__ void layer_dispatch(const fast_args& a, const fast_layer& ly, const float* __restrict__ W, float* __restrict__ ACT,
+                                                   int tt, int n_act)
+    {
+        if (ly.ks == 4) layer_phase<E, 4>(a, ly, W, ACT, tt, n_act);
+        else if (ly.ks == 2) layer_phase<E, 2>(a, ly, W, ACT, tt, n_act);
+        else layer_phase<E, 1>(a, ly, W, ACT, tt, n_act);
     }
 
     // begin an episode of layout l in slot s (reset(spad_x1, lpad_x1), src/game_logic.cpp:143-154) and publish its state
@@ -191,15 +237,13 @@ namespace
                                               float* __restrict__ ACT, int* ctl, double* res_fit, int* res_meta, unsigned long long member, int s)
     {
         const fast_layer& ly = a.layer[a.n_layers - 1];
-        const float* part    = ACT + a.part_off;
-        int action = 0;
-        float vbest = 0.f;
-        for (int o = 0; o < ly.out; ++o)
+        const float* z       = ACT + ly.out_off + s;
+        int action  = 0;
+        float vbest = z[0];
+        for (int o = 1; o < ly.out; ++o)
         {
-            float v = W[ly.b_off + o];
-            for (int k = 0; k < ly.ks; ++k) v += part[((size_t)k * ly.out_pad + o) * a.S + s];
-            v = fast_act(v, a.act);
-            if (o == 0 || v > vbest) vbest = v, action = o;
+            const float v = z[o * a.S];
+            if (v > vbest) vbest = v, action = o;
         }
         ll_lander<float> p{sv.x[s], sv.y[s], sv.vx[s], sv.vy[s], sv.fuel[s]};
         const float cx = sv.cx[s];
@@ -365,17 +409,12 @@ namespace
                 }
                 if (__syncthreads_and(finished)) break;
             }
-            // ---- forward pass: one phase per layer (+ a reduce phase for split-K hidden layers)
+            // ---- forward pass: one phase per layer
             for (int l = 0; l < n_layers; ++l)
             {
                 const fast_layer ly = s_layer[l];
-                if (running) layer_gemm<E>(a, ly, W, ACT, tt, n_act);
+                if (running) layer_dispatch<E>(a, ly, W, ACT, tt, n_act);
                 __syncthreads();
-                if (ly.ks > 1 && !ly.last)
-                {
-                    if (running) layer_reduce(a, ly, W, ACT, tt, n_act);
-                    __syncthreads();
-                }
             }
         }
     }
@@ -419,14 +458,9 @@ namespace
         if (TS > MAX_THREADS) TS = MAX_THREADS;
         a.TS = TS;
 
-        // activation buffers: even / odd ping-pong sized by the widest activation of each parity, then split-K partials
-        int even = 0, odd = 0, part = 0;
-        for (int l = 0; l <= tp.n_layers; ++l)
-        {
-            const int width = l == 0 ? tp.in[0] : tp.out[l - 1];
-            if (l == tp.n_layers) break; // the output layer only produces partial sums
-            ((l & 1) ? odd : even) = std::max((l & 1) ? odd : even, width * a.S);
-        }
+        // activation buffers: even / odd ping-pong sized by the widest activation of each parity, then the output layer's Z
+        int even = 0, odd = 0;
+        for (int l = 0; l < tp.n_layers; ++l) ((l & 1) ? odd : even) = std::max((l & 1) ? odd : even, tp.in[l] * a.S);
         for (int l = 0; l < tp.n_layers; ++l)
         {
             fast_layer& ly = a.layer[l];
@@ -434,16 +468,14 @@ namespace
             ly.last  = l == tp.n_layers - 1;
             ly.nog   = tp.out_pad[l] / FO;
             ly.tiles = Ge * ly.nog;
-            int ks   = 1;
-            while (ly.tiles * ks * 2 <= TS && ly.in / (ks * 2) >= 8) ks *= 2;
-            ly.ks    = ks;
-            ly.klen  = (ly.in + ks - 1) / ks;
+            int ks   = 1; // k-slices per tile: fill the team's threads, keep >= 8 rows per slice, slices of a tile in one warp
+            while (ks < 4 && (TS & 31) == 0 && ly.tiles * ks * 2 <= TS && ly.in / (ks * 2) >= 8) ks *= 2;
+            ly.ks      = ks;
+            ly.klen    = (ly.in + ks - 1) / ks;
             ly.in_off  = (l & 1) ? even : 0;
-            ly.out_off = (l & 1) ? 0 : even;
-            if (ks > 1 || ly.last) part = std::max(part, ks * ly.out_pad * a.S);
+            ly.out_off = ly.last ? even + odd : ((l & 1) ? 0 : even);
         }
-        a.part_off = even + odd;
-        const int act_elems = even + odd + part;
+        const int act_elems = even + odd + tp.out[tp.n_layers - 1] * a.S;
         auto up             = [](int v) { return (v + 127) & ~127; };
         a.off_w             = 128;
         a.off_act           = up(a.off_w + tp.p_dev * 4);
