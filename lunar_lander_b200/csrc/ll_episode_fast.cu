@@ -75,10 +75,12 @@ namespace
 
     __device__ __forceinline__ float fast_act(float z, int act) { return ll_ops<float, LL_MODE_FAST>::act(z, act); }
 
-    // One (episode group, output group, k-slice) register tile: acc[e][j] = sum_k in[k][ge*E + e] * W[k][go*8 + j].
+    // One (episode group, output group, k-slice) register tile: acc[e][j] = sum_k in[k][ge*E + e] * W[k][col(j)], where the
+    // tile's 8 outputs are columns go*4..go*4+3 and half+go*4..half+go*4+3 (half = out_pad/2): the 8 lanes of a quarter-warp
+    // then read 128 contiguous bytes per LDS.128 (no bank conflict) when consecutive lanes hold consecutive output groups.
     // Pointer-increment form: per k two row-pointer bumps, two LDS.128 (weights), E LDS.32 (activations), E*8 FFMA.
     template <int E>
-    __device__ __forceinline__ void gemm_tile(const float* __restrict__ wp, const float* __restrict__ ap, int klen, int out_pad, int S,
+    __device__ __forceinline__ void gemm_tile(const float* __restrict__ wp, const float* __restrict__ ap, int klen, int out_pad, int S, int half,
                                               float (&acc)[E][FO])
     {
 #pragma unroll
@@ -89,7 +91,7 @@ namespace
         for (int k = 0; k < klen; ++k)
         {
             const float4 w0 = *reinterpret_cast<const float4*>(wp);
-            const float4 w1 = *reinterpret_cast<const float4*>(wp + 4);
+            const float4 w1 = *reinterpret_cast<const float4*>(wp + half);
             float av[E];
 #pragma unroll
             for (int e = 0; e < E; ++e) av[e] = ap[e];
@@ -172,7 +174,7 @@ namespace
                                                 int tt, int n_act)
     {
         constexpr int TPW = 32 / KS;
-        const int S = a.S, Ge = a.Ge;
+        const int S = a.S;
         const float* in = ACT + ly.in_off;
         float* outb     = ACT + ly.out_off;
         int tile, stride, ksi = 0;
@@ -190,24 +192,42 @@ namespace
         }
         for (; tile < ly.tiles; tile += stride)
         {
-            const int go = tile / Ge, ge = tile - go * Ge;
-            if (ge * E >= n_act) continue;
-            const int kl = (ly.in - ksi + KS - 1) / KS;
+            const int ge = tile / ly.nog, go = tile - ge * ly.nog; // episode group slowest: active tiles fill whole warps
+            if (ge * E >= n_act) break;
+            const int kl   = (ly.in - ksi + KS - 1) / KS;
+            const int half = ly.out_pad >> 1;
             float acc[E][FO];
-            gemm_tile<E>(W + ly.w_off + ksi * ly.out_pad + go * FO, in + ksi * S + ge * E, kl, KS * ly.out_pad, KS * S, acc);
+            gemm_tile<E>(W + ly.w_off + ksi * ly.out_pad + go * 4, in + ksi * S + ge * E, kl, KS * ly.out_pad, KS * S, half, acc);
             float res[E][FO / KS];
             const int j0   = reduce_scatter<E, KS>(acc, ksi, mask, res);
-            const int o0   = go * FO + j0;
+            const int o0   = go * 4 + (j0 & 3) + ((j0 & 4) ? half : 0); // first owned column (the owned ones are consecutive)
             const float* b = W + ly.b_off + o0;
             float* out     = outb + o0 * S + ge * E;
+            if constexpr (KS == 1)
+            { // owns both halves: columns go*4 + j and half + go*4 + j
 #pragma unroll
-            for (int j = 0; j < FO / KS; ++j)
-                if (o0 + j < ly.out)
+                for (int j = 0; j < FO; ++j)
                 {
-                    const float bj = b[j];
+                    const int o = go * 4 + (j & 3) + ((j & 4) ? half : 0);
+                    if (o < ly.out)
+                    {
+                        const float bj = W[ly.b_off + o];
 #pragma unroll
-                    for (int e = 0; e < E; ++e) out[j * S + e] = fast_act(res[e][j] + bj, a.act);
+                        for (int e = 0; e < E; ++e) outb[o * S + ge * E + e] = fast_act(res[e][j] + bj, a.act);
+                    }
                 }
+            }
+            else
+            {
+#pragma unroll
+                for (int j = 0; j < FO / KS; ++j)
+                    if (o0 + j < ly.out)
+                    {
+                        const float bj = b[j];
+#pragma unroll
+                        for (int e = 0; e < E; ++e) out[j * S + e] = fast_act(res[e][j] + bj, a.act);
+                    }
+            }
         }
     }
 
