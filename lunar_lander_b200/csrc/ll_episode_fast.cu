@@ -4,29 +4,39 @@
 // GameLogicCpp<T> src/game_logic.cpp:124-388, the ma-libs feedforward call :501-502), with free summation order,
 // fused multiply-add and tanh.approx.f32 — judged on outcome rates, not on bit patterns (tests/test_gpu_parity.py).
 //
-// Why a different mapping: a lane-per-episode GEMV delivers one shared-memory word per FMA and
-// shared memory returns 32 words/clk/SM against 128 FMA lanes/clk/SM, i.e. <= 25 % of the FP32 pipe.  All L layouts of
-// a member share its weights, so one forward pass for a member is a small GEMM  D[S x out] = A[S x in] * W^T[in x out]
-// (S = concurrent episode slots).  A TEAM of threads owns one member at a time; each thread computes a register tile of
-// E episodes x 8 outputs (E*8 FMAs per E+8 words fetched), layers wide in K are split over k-slices and reduced
-// through shared memory.  Per step: env phase (one thread per slot: argmax -> lander update -> penalties -> next
-// state) then one phase per layer, separated by CTA barriers.  A member's row is staged once by a TMA bulk copy
-// (cp.async.bulk + mbarrier); teams pull members from a global queue, slots pull the member's layouts from a
-// shared-memory counter, so episode lengths of 9..max_steps steps balance dynamically.
+// Mapping.  A lane-per-episode GEMV fetches one shared-memory word per FMA; shared memory returns 32
+// words/clk/SM against 128 FMA lanes/clk/SM, i.e. <= 25 % of the FP32 pipe.  All L layouts of a member share its
+// weights, so a forward pass is a small GEMM D[slots x out] = A[slots x in] * W^T[in x out]: each thread computes a
+// register tile of E episode slots x 8 outputs (E*8 FFMA per E+8 words), K-deep layers are split over k-slices that
+// live in one warp and are reduced by shuffles.
+//
+// Episodes last 9..max_steps steps, so a member alone leaves most of its slots idle for most of its life.  A CTA
+// therefore keeps M members resident (their rows staged once each by a TMA bulk copy, cp.async.bulk + mbarrier) and owns
+// a POOL of G slot groups (E slots each) that the members share: a group belongs to one member at a time, slots pull
+// that member's next layout when their episode ends, groups drained by a finishing member go to the oldest member that
+// still has layouts to start, and a member whose episodes are all done hands its buffer to the next member of the
+// global queue.  Per step: env phase (one thread per slot: argmax -> lander update -> penalties -> next state / next
+// layout), then one phase per layer over the tiles of all live groups, separated by CTA barriers.
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+
 #include "ll_env.cuh"
 
 namespace
 {
-    constexpr int FO          = 8;   // outputs per thread tile
-    constexpr int MAX_THREADS = 256; // per CTA
-    constexpr int MAX_RES     = 256; // layouts whose per-episode results are kept in shared memory
+    constexpr int FO       = 8;   // outputs per thread tile
+    constexpr int MAX_M    = 8;   // resident members per CTA
+    constexpr int MAX_G    = 32;  // slot groups per CTA
+    constexpr int MAX_RES  = 256; // layouts whose per-episode results are kept in shared memory
+    constexpr int MAX_INIT = MAX_G * 8;
 
     struct fast_layer
     {
         int in, out, out_pad, w_off, b_off; // topology (element offsets inside a member row)
-        int nog, tiles, ks, klen;           // output groups, (episode group x output group) tiles, k-slices, k per slice
-        int in_off, out_off;                // element offsets of the activation buffers inside the team's region
-        int last;                           // output layer: its activations go to the Z buffer of the env phase
+        int nog, ks;                        // output groups of 8, k-slices per tile
+        int in_off, out_off;                // element offsets of the activation buffers
+        int last;
     };
 
     struct fast_args
@@ -39,22 +49,33 @@ namespace
         int* ep_steps;
         double* ep_fit;
         unsigned int* queue;
+        unsigned long long* prof;
         int n_layers, act, p_dev;
-        int TS, NT, Ge, S;                                     // threads per team, teams per CTA, episode groups, slots = E * Ge
-        int off_w, off_act, off_slot, off_res, team_bytes;     // byte offsets inside a team's shared-memory region
+        int M, G, S, threads;                           // resident members, slot groups, slots = G * E, CTA size
+        int w_stride;                                   // floats between weight buffers
+        int off_ctl, off_w, off_act, off_slot, off_res; // byte offsets inside the CTA's shared memory
         int res_in_smem;
         fast_layer layer[LL_MAX_LAYERS];
     };
 
-    // per-team control words (ints at byte 16 of the team region)
     enum
     {
-        C_NEXT_LAYOUT = 0,
-        C_N_ACTIVE    = 1,
-        C_HAS_MEMBER  = 2,
-        C_MEMBER_LO   = 3,
-        C_MEMBER_HI   = 4,
-        C_DIRTY       = 5
+        ST_EMPTY   = 0,
+        ST_LOADING = 1,
+        ST_ACTIVE  = 2
+    };
+
+    struct pool_ctl
+    {
+        uint64_t bar[MAX_M];
+        unsigned long long member[MAX_M];
+        int status[MAX_M], next_layout[MAX_M], inflight[MAX_M], parity[MAX_M];
+        unsigned int age[MAX_M];
+        unsigned int age_counter;
+        int dirty, n_g, queue_done, exit_flag, n_init;
+        int gmem[MAX_G];  // group -> member buffer, -1 = free
+        int glist[MAX_G]; // groups that hold at least one live slot
+        int init_slot[MAX_INIT], init_layout[MAX_INIT];
     };
 
     struct slot_view
@@ -75,7 +96,7 @@ namespace
 
     __device__ __forceinline__ float fast_act(float z, int act) { return ll_ops<float, LL_MODE_FAST>::act(z, act); }
 
-    // One (episode group, output group, k-slice) register tile: acc[e][j] = sum_k in[k][ge*E + e] * W[k][col(j)], where the
+    // One (episode group, output group, k-slice) register tile: acc[e][j] = sum_k in[k][g*E + e] * W[k][col(j)], where the
     // tile's 8 outputs are columns go*4..go*4+3 and half+go*4..half+go*4+3 (half = out_pad/2): the 8 lanes of a quarter-warp
     // then read 128 contiguous bytes per LDS.128 (no bank conflict) when consecutive lanes hold consecutive output groups.
     // Pointer-increment form: per k two row-pointer bumps, two LDS.128 (weights), E LDS.32 (activations), E*8 FFMA.
@@ -165,44 +186,44 @@ namespace
         }
     }
 
-    // One layer for one team.  Slots are kept compacted (active slots are [0, n_act)) and a thread's E slots are contiguous
-    // (slot = ge*E + e), so tiles of episode groups past n_act are skipped.  KS k-slices of a tile (rows k = KS*i + ksi)
-    // live in one warp and are reduced by shuffles; the owners add the bias, apply the activation and store
+
+    // One layer over the tiles of all live groups.  tile -> (live group gi, output group go), go fastest so that a
+    // quarter-warp shares the slot group (activation broadcast) and walks consecutive weight columns.  KS k-slices of a
+    // tile (rows k = KS*i + ksi) are reduced by shuffles; the owners add the bias, apply the activation and store
     // out[o][slot].  The output layer stores into the Z buffer the env phase takes its argmax from.
     template <int E, int KS>
-    __device__ __forceinline__ void layer_phase(const fast_args& a, const fast_layer& ly, const float* __restrict__ W, float* __restrict__ ACT,
-                                                int tt, int n_act)
+    __device__ __forceinline__ void layer_phase(const fast_args& a, const fast_layer& ly, const pool_ctl* ctl, const float* __restrict__ W0,
+                                                float* __restrict__ ACT, int tid, int n_g)
     {
         constexpr int TPW = 32 / KS;
         const int S = a.S;
         const float* in = ACT + ly.in_off;
         float* outb     = ACT + ly.out_off;
+        const int tiles = n_g * ly.nog;
         int tile, stride, ksi = 0;
         unsigned mask = 0xffffffffu;
-        if constexpr (KS == 1) tile = tt, stride = a.TS;
+        if constexpr (KS == 1) tile = tid, stride = a.threads;
         else
         {
-            const int lane = tt & 31, q = lane & (TPW - 1);
+            const int lane = tid & 31, q = lane & (TPW - 1);
             ksi    = lane / TPW;
-            tile   = (tt >> 5) * TPW + q;
-            stride = (a.TS >> 5) * TPW;
+            tile   = (tid >> 5) * TPW + q;
+            stride = (a.threads >> 5) * TPW;
             mask   = 0;
 #pragma unroll
             for (int i = 0; i < KS; ++i) mask |= 1u << (i * TPW + q);
         }
-        for (; tile < ly.tiles; tile += stride)
+        const int half = ly.out_pad >> 1;
+        for (; tile < tiles; tile += stride)
         {
-            const int ge = tile / ly.nog, go = tile - ge * ly.nog; // episode group slowest: active tiles fill whole warps
-            if (ge * E >= n_act) break;
+            const int gi = tile / ly.nog, go = tile - gi * ly.nog;
+            const int g  = ctl->glist[gi];
+            const float* W = W0 + (size_t)ctl->gmem[g] * a.w_stride;
             const int kl   = (ly.in - ksi + KS - 1) / KS;
-            const int half = ly.out_pad >> 1;
             float acc[E][FO];
-            gemm_tile<E>(W + ly.w_off + ksi * ly.out_pad + go * 4, in + ksi * S + ge * E, kl, KS * ly.out_pad, KS * S, half, acc);
+            gemm_tile<E>(W + ly.w_off + ksi * ly.out_pad + go * 4, in + ksi * S + g * E, kl, KS * ly.out_pad, KS * S, half, acc);
             float res[E][FO / KS];
-            const int j0   = reduce_scatter<E, KS>(acc, ksi, mask, res);
-            const int o0   = go * 4 + (j0 & 3) + ((j0 & 4) ? half : 0); // first owned column (the owned ones are consecutive)
-            const float* b = W + ly.b_off + o0;
-            float* out     = outb + o0 * S + ge * E;
+            const int j0 = reduce_scatter<E, KS>(acc, ksi, mask, res);
             if constexpr (KS == 1)
             { // owns both halves: columns go*4 + j and half + go*4 + j
 #pragma unroll
@@ -213,12 +234,15 @@ namespace
                     {
                         const float bj = W[ly.b_off + o];
 #pragma unroll
-                        for (int e = 0; e < E; ++e) outb[o * S + ge * E + e] = fast_act(res[e][j] + bj, a.act);
+                        for (int e = 0; e < E; ++e) outb[o * S + g * E + e] = fast_act(res[e][j] + bj, a.act);
                     }
                 }
             }
             else
             {
+                const int o0   = go * 4 + (j0 & 3) + ((j0 & 4) ? half : 0); // first owned column (the owned ones are consecutive)
+                const float* b = W + ly.b_off + o0;
+                float* out     = outb + o0 * S + g * E;
 #pragma unroll
                 for (int j = 0; j < FO / KS; ++j)
                     if (o0 + j < ly.out)
@@ -232,19 +256,19 @@ namespace
     }
 
     template <int E>
-    __device__ __forceinline__ void layer_dispatch(const fast_args& a, const fast_layer& ly, const float* __restrict__ W, float* __restrict__ ACT,
-                                                   int tt, int n_act)
+    __device__ __forceinline__ void layer_dispatch(const fast_args& a, const fast_layer& ly, const pool_ctl* ctl, const float* __restrict__ W0,
+                                                   float* __restrict__ ACT, int tid, int n_g)
     {
-        if (ly.ks == 4) layer_phase<E, 4>(a, ly, W, ACT, tt, n_act);
-        else if (ly.ks == 2) layer_phase<E, 2>(a, ly, W, ACT, tt, n_act);
-        else layer_phase<E, 1>(a, ly, W, ACT, tt, n_act);
+        if (ly.ks == 4) layer_phase<E, 4>(a, ly, ctl, W0, ACT, tid, n_g);
+        else if (ly.ks == 2) layer_phase<E, 2>(a, ly, ctl, W0, ACT, tid, n_g);
+        else layer_phase<E, 1>(a, ly, ctl, W0, ACT, tid, n_g);
     }
 
     // begin an episode of layout l in slot s (reset(spad_x1, lpad_x1), src/game_logic.cpp:143-154) and publish its state
     __device__ __forceinline__ void slot_begin(const fast_args& a, const ll_env<float>& env, slot_view& sv, float* A0, int s, int l)
     {
         const ll_layout<float> lay = a.layouts[l];
-        sv.layout[s] = l | (lay.dir << 30);
+        sv.layout[s] = l;
         sv.cx[s] = lay.center_x, sv.lpad[s] = lay.lpad_x1, sv.lpad_r[s] = lay.lpad_right;
         ll_lander<float> p{lay.init_x, env.y0, env.vx0, env.vy0, env.max_fuel};
         sv.x[s] = p.x, sv.y[s] = p.y, sv.vx[s] = p.vx, sv.vy[s] = p.vy, sv.fuel[s] = p.fuel;
@@ -252,86 +276,144 @@ namespace
         ll_get_state<float, LL_MODE_FAST>(env, p, lay.center_x, A0 + s, a.S);
     }
 
-    // env phase of one active slot: output layer reduce -> argmax -> update -> penalties -> next state / next layout
-    __device__ __forceinline__ void slot_step(const fast_args& a, const ll_env<float>& env, slot_view& sv, const float* __restrict__ W,
-                                              float* __restrict__ ACT, int* ctl, double* res_fit, int* res_meta, unsigned long long member, int s)
+    // First layer (5 inputs) for one slot by its quad of lanes: lane j computes the 8-output chunks j, j+4, ... from the
+    // state held in registers and stores the activations A1[o][slot].
+    __device__ __forceinline__ void first_layer_quad(const fast_args& a, const fast_layer& l0, const float* __restrict__ W, float* __restrict__ ACT,
+                                                     const float (&st)[5], int s, int j)
     {
-        const fast_layer& ly = a.layer[a.n_layers - 1];
-        const float* z       = ACT + ly.out_off + s;
-        int action  = 0;
-        float vbest = z[0];
-        for (int o = 1; o < ly.out; ++o)
+        float* out = ACT + l0.out_off + s;
+        for (int c = j; c < l0.nog; c += 4)
         {
-            const float v = z[o * a.S];
-            if (v > vbest) vbest = v, action = o;
+            const float* wp = W + l0.w_off + c * FO;
+            const float4 b0 = *reinterpret_cast<const float4*>(W + l0.b_off + c * FO);
+            const float4 b1 = *reinterpret_cast<const float4*>(W + l0.b_off + c * FO + 4);
+            float acc[FO]   = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+            for (int k = 0; k < 5; ++k)
+            {
+                const float4 w0 = *reinterpret_cast<const float4*>(wp + k * l0.out_pad);
+                const float4 w1 = *reinterpret_cast<const float4*>(wp + k * l0.out_pad + 4);
+                acc[0] = fmaf(st[k], w0.x, acc[0]), acc[1] = fmaf(st[k], w0.y, acc[1]), acc[2] = fmaf(st[k], w0.z, acc[2]);
+                acc[3] = fmaf(st[k], w0.w, acc[3]), acc[4] = fmaf(st[k], w1.x, acc[4]), acc[5] = fmaf(st[k], w1.y, acc[5]);
+                acc[6] = fmaf(st[k], w1.z, acc[6]), acc[7] = fmaf(st[k], w1.w, acc[7]);
+            }
+#pragma unroll
+            for (int i = 0; i < FO; ++i)
+                if (c * FO + i < l0.out) out[(c * FO + i) * a.S] = fast_act(acc[i], a.act);
         }
+    }
+
+    // The light phase of one live slot, executed by a quad of consecutive lanes (j = lane & 3):
+    //   output layer (k split over the quad, butterfly reduce) -> argmax -> lander update -> penalties -> episode end
+    //   handling (results, next layout or retirement) -> next state -> first layer.
+    // The lander arithmetic is done redundantly by the four lanes (same inputs, same results); lane 0 owns the writes.
+    __device__ __forceinline__ void light_slot(const fast_args& a, const fast_layer& l0, const fast_layer& ll, const ll_env<float>& env, slot_view& sv,
+                                               const float* __restrict__ W, float* __restrict__ ACT, pool_ctl* ctl, double* res_fit, int* res_meta,
+                                               int mb, int s, int j, unsigned qmask)
+    {
+        // ---- output layer: z[o] = act(b[o] + sum_k A[k][s] * W[k][o]), out <= 8
+        float z[FO] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        {
+            const float* ap = ACT + ll.in_off + s;
+            const float* wp = W + ll.w_off;
+            for (int k = j; k < ll.in; k += 4)
+            {
+                const float av  = ap[k * a.S];
+                const float4 w0 = *reinterpret_cast<const float4*>(wp + k * ll.out_pad);
+                z[0] = fmaf(av, w0.x, z[0]), z[1] = fmaf(av, w0.y, z[1]), z[2] = fmaf(av, w0.z, z[2]), z[3] = fmaf(av, w0.w, z[3]);
+                if (ll.out > 4)
+                {
+                    const float4 w1 = *reinterpret_cast<const float4*>(wp + k * ll.out_pad + 4);
+                    z[4] = fmaf(av, w1.x, z[4]), z[5] = fmaf(av, w1.y, z[5]), z[6] = fmaf(av, w1.z, z[6]), z[7] = fmaf(av, w1.w, z[7]);
+                }
+            }
+        }
+        int action  = 0;
+        float vbest = 0.f;
+#pragma unroll
+        for (int o = 0; o < FO; ++o)
+            if (o < ll.out)
+            {
+                float v = z[o];
+                v += __shfl_xor_sync(qmask, v, 1);
+                v += __shfl_xor_sync(qmask, v, 2);
+                v = fast_act(v + W[ll.b_off + o], a.act);
+                if (o == 0 || v > vbest) vbest = v, action = o;
+            }
+        // ---- lander update (src/game_logic.cpp:295-320 through ll_env.cuh)
         ll_lander<float> p{sv.x[s], sv.y[s], sv.vx[s], sv.vy[s], sv.fuel[s]};
-        const float cx = sv.cx[s];
-        int steps      = sv.steps[s];
+        float cx  = sv.cx[s];
+        int steps = sv.steps[s];
         bool landed, success;
         float dist;
-        const float sp = ll_env_step<float, LL_MODE_FAST>(env, p, action, steps == 0, cx, sv.lpad[s], sv.lpad_r[s], &landed, &success, &dist);
+        const float sp   = ll_env_step<float, LL_MODE_FAST>(env, p, action, steps == 0, cx, sv.lpad[s], sv.lpad_r[s], &landed, &success, &dist);
         const double acc = sv.acc[s] + (double)sp;
         ++steps;
-        float* A0 = ACT + a.layer[0].in_off;
         if (landed || steps >= a.max_steps)
         {
-            const float term = ll_terminal_penalty<float, LL_MODE_FAST>(env, p, steps, landed, success, dist);
-            const double fit = (double)term + acc;
-            const int lw     = sv.layout[s];
-            const int layout = lw & 0x3fffffff;
-            const int meta   = steps | (landed ? (1 << 28) : 0) | ((landed && !success) ? (1 << 29) : 0) | (success ? (1 << 30) : 0);
-            if (a.res_in_smem) res_fit[layout] = fit, res_meta[layout] = meta;
-            if (a.ep_steps)
+            int nl = 0;
+            if (j == 0)
             {
-                a.ep_steps[member * (size_t)a.n_layouts + layout] = meta;
-                a.ep_fit[member * (size_t)a.n_layouts + layout]   = fit;
+                const float term = ll_terminal_penalty<float, LL_MODE_FAST>(env, p, steps, landed, success, dist);
+                const double fit = (double)term + acc;
+                const int layout = sv.layout[s];
+                const int meta   = steps | (landed ? (1 << 28) : 0) | ((landed && !success) ? (1 << 29) : 0) | (success ? (1 << 30) : 0);
+                if (a.res_in_smem) res_fit[mb * a.n_layouts + layout] = fit, res_meta[mb * a.n_layouts + layout] = meta;
+                if (a.ep_steps)
+                {
+                    const unsigned long long member = ctl->member[mb];
+                    a.ep_steps[member * (size_t)a.n_layouts + layout] = meta;
+                    a.ep_fit[member * (size_t)a.n_layouts + layout]   = fit;
+                }
+                nl = atomicAdd(&ctl->next_layout[mb], 1);
             }
-            const int nl = atomicAdd(&ctl[C_NEXT_LAYOUT], 1);
-            if (nl < a.n_layouts) slot_begin(a, env, sv, A0, s, nl);
-            else
+            nl = __shfl_sync(qmask, nl, 0, 4);
+            if (nl >= a.n_layouts)
+            { // retired: the manager repacks / hands the group over before the next forward pass
+                if (j == 0)
+                {
+                    sv.active[s] = 0;
+                    atomicSub(&ctl->inflight[mb], 1);
+                    ctl->dirty = 1;
+                }
+                return;
+            }
+            const ll_layout<float> lay = a.layouts[nl]; // reset(spad_x1, lpad_x1): src/game_logic.cpp:143-154
+            p  = ll_lander<float>{lay.init_x, env.y0, env.vx0, env.vy0, env.max_fuel};
+            cx = lay.center_x;
+            if (j == 0)
             {
-                sv.active[s] = 0;
-                ctl[C_DIRTY] = 1; // compacted by the team leader before the next forward pass
+                sv.layout[s] = nl, sv.cx[s] = cx, sv.lpad[s] = lay.lpad_x1, sv.lpad_r[s] = lay.lpad_right;
+                sv.x[s] = p.x, sv.y[s] = p.y, sv.vx[s] = p.vx, sv.vy[s] = p.vy, sv.fuel[s] = p.fuel;
+                sv.steps[s] = 0, sv.acc[s] = 0.0;
             }
-            return;
         }
-        sv.x[s] = p.x, sv.y[s] = p.y, sv.vx[s] = p.vx, sv.vy[s] = p.vy, sv.fuel[s] = p.fuel;
-        sv.steps[s] = steps, sv.acc[s] = acc;
-        ll_get_state<float, LL_MODE_FAST>(env, p, cx, A0 + s, a.S);
-    }
-
-    // Keep the active slots packed in [0, n_act): holes left by finished episodes are filled from the top.  Rare (at most
-    // once per finished episode), done serially by the team leader; the moved slot's input column is rebuilt.
-    __device__ void team_compact(const fast_args& a, const ll_env<float>& env, slot_view& sv, float* A0, int* ctl)
-    {
-        int i = 0, j = ctl[C_N_ACTIVE] - 1;
-        for (;;)
+        else if (j == 0)
         {
-            while (i <= j && sv.active[i]) ++i;
-            while (j >= i && !sv.active[j]) --j;
-            if (i >= j) break;
-            sv.acc[i] = sv.acc[j];
-            sv.x[i] = sv.x[j], sv.y[i] = sv.y[j], sv.vx[i] = sv.vx[j], sv.vy[i] = sv.vy[j], sv.fuel[i] = sv.fuel[j];
-            sv.cx[i] = sv.cx[j], sv.lpad[i] = sv.lpad[j], sv.lpad_r[i] = sv.lpad_r[j];
-            sv.steps[i] = sv.steps[j], sv.layout[i] = sv.layout[j];
-            sv.active[i] = 1, sv.active[j] = 0;
-            for (int q = 0; q < a.layer[0].in; ++q) A0[q * a.S + i] = A0[q * a.S + j];
+            sv.x[s] = p.x, sv.y[s] = p.y, sv.vx[s] = p.vx, sv.vy[s] = p.vy, sv.fuel[s] = p.fuel;
+            sv.steps[s] = steps, sv.acc[s] = acc;
         }
-        ctl[C_N_ACTIVE] = j + 1; // j is the last active slot (or -1)
-        ctl[C_DIRTY]    = 0;
+        float st[5];
+        ll_get_state<float, LL_MODE_FAST>(env, p, cx, st, 1);
+        if (j == 0)
+        {
+            float* A0 = ACT + l0.in_off + s;
+#pragma unroll
+            for (int i = 0; i < 5; ++i) A0[i * a.S] = st[i];
+        }
+        first_layer_quad(a, l0, W, ACT, st, s, j);
     }
 
-    // per-member totals in layout order (src/nn_engine_trainer.cpp:518-530), by the team leader
-    __device__ void member_finalize(const fast_args& a, const ll_env<float>& env, const double* res_fit, const int* res_meta,
+    // per-member totals in layout order (src/nn_engine_trainer.cpp:518-530)
+    __device__ void member_finalize(const fast_args& a, const ll_env<float>& env, const double* res_fit, const int* res_meta, int mb,
                                     unsigned long long member)
     {
         double total = 0.0, total_steps = 0.0;
         float bonus0 = 0.f, bonus1 = 0.f;
         for (int l = 0; l < a.n_layouts; ++l)
         {
-            const int meta   = a.res_in_smem ? res_meta[l] : a.ep_steps[member * (size_t)a.n_layouts + l];
-            const double fit = a.res_in_smem ? res_fit[l] : a.ep_fit[member * (size_t)a.n_layouts + l];
+            const int meta   = a.res_in_smem ? res_meta[mb * a.n_layouts + l] : a.ep_steps[member * (size_t)a.n_layouts + l];
+            const double fit = a.res_in_smem ? res_fit[mb * a.n_layouts + l] : a.ep_fit[member * (size_t)a.n_layouts + l];
             total += fit;
             total_steps += (double)(meta & 0x0fffffff);
             if (meta & (1 << 30))
@@ -346,113 +428,216 @@ namespace
         a.steps[member]   = total_steps;
     }
 
+    __device__ __forceinline__ void slot_move(const fast_args& a, slot_view& sv, float* A0, int dst, int src)
+    {
+        sv.acc[dst] = sv.acc[src];
+        sv.x[dst] = sv.x[src], sv.y[dst] = sv.y[src], sv.vx[dst] = sv.vx[src], sv.vy[dst] = sv.vy[src], sv.fuel[dst] = sv.fuel[src];
+        sv.cx[dst] = sv.cx[src], sv.lpad[dst] = sv.lpad[src], sv.lpad_r[dst] = sv.lpad_r[src];
+        sv.steps[dst] = sv.steps[src], sv.layout[dst] = sv.layout[src];
+        sv.active[dst] = 1, sv.active[src] = 0;
+        for (int q = 0; q < a.layer[0].in; ++q) A0[q * a.S + dst] = A0[q * a.S + src];
+    }
+
+    // The pool manager (thread 0, between two barriers, only after an episode ended without a successor): finalize
+    // members whose episodes are all done, repack each member's live slots into the fewest groups, free drained groups,
+    // pull new members into empty buffers (TMA), give free groups to the oldest member that still has layouts to start.
     template <int E>
-    __global__ void __launch_bounds__(MAX_THREADS) ll_episode_fast_kernel(const __grid_constant__ ll_env<float> env, const __grid_constant__ fast_args a)
+    __device__ void pool_manage(const fast_args& a, const ll_env<float>& env, pool_ctl* ctl, slot_view& sv, float* A0, float* W0, const double* res_fit,
+                                const int* res_meta)
+    {
+        const int L = a.n_layouts, M = a.M, G = a.G;
+        ctl->dirty = 0, ctl->n_init = 0;
+        for (int mb = 0; mb < M; ++mb)
+            if (ctl->status[mb] == ST_ACTIVE && ctl->inflight[mb] == 0 && ctl->next_layout[mb] >= L)
+            {
+                member_finalize(a, env, res_fit, res_meta, mb, ctl->member[mb]);
+                ctl->status[mb] = ST_EMPTY;
+            }
+        for (int mb = 0; mb < M; ++mb)
+        {
+            if (ctl->status[mb] == ST_EMPTY) continue;
+            int gl[MAX_G], ng = 0, live = 0;
+            for (int g = 0; g < G; ++g)
+                if (ctl->gmem[g] == mb)
+                {
+                    gl[ng++] = g;
+                    for (int e = 0; e < E; ++e) live += sv.active[g * E + e];
+                }
+            if (ng > 0 && live <= E * (ng - 1))
+            { // holes at the front are filled from the back: the member's last groups drain
+                int i = 0, j = ng * E - 1;
+                for (;;)
+                {
+                    while (i <= j && sv.active[gl[i / E] * E + i % E]) ++i;
+                    while (j >= i && !sv.active[gl[j / E] * E + j % E]) --j;
+                    if (i >= j) break;
+                    slot_move(a, sv, A0, gl[i / E] * E + i % E, gl[j / E] * E + j % E);
+                }
+            }
+        }
+        for (int g = 0; g < G; ++g)
+            if (ctl->gmem[g] >= 0)
+            {
+                int live = 0;
+                for (int e = 0; e < E; ++e) live += sv.active[g * E + e];
+                if (!live) ctl->gmem[g] = -1;
+            }
+        for (int mb = 0; mb < M; ++mb)
+            if (ctl->status[mb] == ST_EMPTY && !ctl->queue_done)
+            {
+                const unsigned long long m = (unsigned long long)atomicAdd(a.queue, 1u);
+                if (m < a.n_members)
+                {
+                    ctl->status[mb] = ST_LOADING, ctl->member[mb] = m, ctl->next_layout[mb] = 0, ctl->inflight[mb] = 0;
+                    ctl->age[mb] = ++ctl->age_counter;
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    ll_mbar_expect_tx(&ctl->bar[mb], (uint32_t)a.p_dev * 4u);
+                    ll_bulk_g2s(W0 + (size_t)mb * a.w_stride, a.params + m * (size_t)a.p_dev, (uint32_t)a.p_dev * 4u, &ctl->bar[mb]);
+                }
+                else ctl->queue_done = 1;
+            }
+        for (int g = 0; g < G; ++g)
+        {
+            if (ctl->gmem[g] >= 0) continue;
+            int best = -1;
+            for (int mb = 0; mb < M; ++mb)
+                if (ctl->status[mb] != ST_EMPTY && ctl->next_layout[mb] < L && (best < 0 || ctl->age[mb] < ctl->age[best])) best = mb;
+            if (best < 0) break;
+            ctl->gmem[g] = best;
+            for (int e = 0; e < E; ++e)
+            {
+                const int s = g * E + e, nl = ctl->next_layout[best];
+                if (nl < L)
+                {
+                    ctl->next_layout[best] = nl + 1, ctl->inflight[best] += 1;
+                    ctl->init_slot[ctl->n_init] = s, ctl->init_layout[ctl->n_init] = nl, ctl->n_init += 1;
+                }
+                else sv.active[s] = 0;
+            }
+        }
+        int n_g = 0, busy = 0;
+        for (int g = 0; g < G; ++g)
+            if (ctl->gmem[g] >= 0) ctl->glist[n_g++] = g;
+        ctl->n_g = n_g;
+        for (int mb = 0; mb < M; ++mb) busy += ctl->status[mb] != ST_EMPTY;
+        ctl->exit_flag = (busy == 0 && ctl->queue_done) ? 1 : 0;
+    }
+
+    // PROF: thread 0 accumulates clock64() per phase (env, manage, layers 0..) and the live-group count, and adds them
+    // to a.prof at exit — a development aid behind LL_FAST_PROF, compiled out of the production instantiation.
+    template <int E, bool PROF>
+    __global__ void __launch_bounds__(384) ll_episode_fast_kernel(const __grid_constant__ ll_env<float> env, const __grid_constant__ fast_args a)
     {
         extern __shared__ __align__(128) unsigned char smem_raw[];
-        __shared__ fast_layer s_layer[LL_MAX_LAYERS]; // the layer table in shared memory: indexed reads of kernel parameters are slow
-        const int tid = threadIdx.x, team = tid / a.TS, tt = tid - team * a.TS;
-        unsigned char* tb = smem_raw + (size_t)team * a.team_bytes;
-        uint64_t* bar     = reinterpret_cast<uint64_t*>(tb);
-        int* ctl          = reinterpret_cast<int*>(tb + 16);
-        float* W          = reinterpret_cast<float*>(tb + a.off_w);
-        float* ACT        = reinterpret_cast<float*>(tb + a.off_act);
-        slot_view sv(tb + a.off_slot, a.S);
-        double* res_fit = reinterpret_cast<double*>(tb + a.off_res);
-        int* res_meta   = reinterpret_cast<int*>(res_fit + (a.res_in_smem ? a.n_layouts : 0));
+        __shared__ fast_layer s_layer[LL_MAX_LAYERS]; // indexed reads of kernel parameters are slow: keep the table in shared memory
+        const int tid = threadIdx.x, threads = a.threads;
+        pool_ctl* ctl = reinterpret_cast<pool_ctl*>(smem_raw + a.off_ctl);
+        float* W0     = reinterpret_cast<float*>(smem_raw + a.off_w);
+        float* ACT    = reinterpret_cast<float*>(smem_raw + a.off_act);
+        slot_view sv(smem_raw + a.off_slot, a.S);
+        double* res_fit = reinterpret_cast<double*>(smem_raw + a.off_res);
+        int* res_meta   = reinterpret_cast<int*>(res_fit + (a.res_in_smem ? a.M * a.n_layouts : 0));
         float* A0       = ACT + a.layer[0].in_off;
-        const uint32_t row_bytes = (uint32_t)a.p_dev * sizeof(float);
-        const int n_layers       = a.n_layers;
+        const int n_layers = a.n_layers;
 
-        for (int i = tid; i < n_layers; i += blockDim.x) s_layer[i] = a.layer[i];
-        if (tt == 0)
+        for (int i = tid; i < n_layers; i += threads) s_layer[i] = a.layer[i];
+        for (int i = tid; i < (a.off_slot - a.off_act) / 4; i += threads) ACT[i] = 0.f;
+        for (int i = tid; i < a.S; i += threads) sv.active[i] = 0;
+        if (tid == 0)
         {
-            ll_mbar_init(bar, 1);
-            ctl[C_N_ACTIVE] = 0, ctl[C_HAS_MEMBER] = 0, ctl[C_NEXT_LAYOUT] = 0, ctl[C_DIRTY] = 0;
+            for (int mb = 0; mb < a.M; ++mb)
+            {
+                ll_mbar_init(&ctl->bar[mb], 1);
+                ctl->status[mb] = ST_EMPTY, ctl->parity[mb] = 0, ctl->inflight[mb] = 0, ctl->next_layout[mb] = 0, ctl->age[mb] = 0;
+            }
+            for (int g = 0; g < a.G; ++g) ctl->gmem[g] = -1;
+            ctl->age_counter = 0, ctl->dirty = 1, ctl->n_g = 0, ctl->queue_done = 0, ctl->exit_flag = 0, ctl->n_init = 0;
         }
         __syncthreads();
-        uint32_t phase            = 0;
-        bool running              = false; // the team holds a member whose episodes are in flight
-        bool finished             = false; // the queue is exhausted for this team
-        unsigned long long member = 0;
-        int n_act                 = 0;
 
+        long long pc[4 + LL_MAX_LAYERS] = {0}, t0 = 0;
+        if (PROF && tid == 0) t0 = clock64();
+#define LL_PROF_MARK(i)                                                                                              \
+    if (PROF && tid == 0)                                                                                            \
+    {                                                                                                                \
+        const long long t1 = clock64();                                                                              \
+        pc[i] += t1 - t0, t0 = t1;                                                                                   \
+    }
         for (;;)
         {
-            // ---- env phase: one thread per active slot
-            if (running)
-                for (int s = tt; s < n_act; s += a.TS) slot_step(a, env, sv, W, ACT, ctl, res_fit, res_meta, member, s);
-            __syncthreads();
-            const bool dirty = running && ctl[C_DIRTY] != 0;
-            if (__syncthreads_or(dirty || (!finished && !running)))
+            int n_g = ctl->n_g;
+            if (PROF && tid == 0) pc[2] += 1, pc[3] += n_g;
+            // ---- light phase: a quad of lanes per slot of the live groups (output layer -> env -> first layer)
+            for (int i = tid; i < n_g * E * 4; i += threads)
             {
-                // ---- rare path: compaction after finished episodes; member hand-over when none is left
-                if (dirty && tt == 0) team_compact(a, env, sv, A0, ctl);
-                __syncthreads();
-                if (running) n_act = ctl[C_N_ACTIVE];
-                const bool need = !finished && (!running || n_act == 0);
-                if (need && tt == 0)
-                {
-                    if (running) member_finalize(a, env, res_fit, res_meta, member);
-                    const unsigned long long m = (unsigned long long)atomicAdd(a.queue, 1u);
-                    if (m < a.n_members)
-                    {
-                        ctl[C_HAS_MEMBER] = 1, ctl[C_MEMBER_LO] = (int)(unsigned int)m, ctl[C_MEMBER_HI] = (int)(unsigned int)(m >> 32);
-                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                        ll_mbar_expect_tx(bar, row_bytes);
-                        ll_bulk_g2s(W, a.params + m * (size_t)a.p_dev, row_bytes, bar);
-                    }
-                    else ctl[C_HAS_MEMBER] = 0;
-                }
-                __syncthreads();
-                if (need)
-                {
-                    if (ctl[C_HAS_MEMBER])
-                    {
-                        member  = (unsigned long long)(unsigned int)ctl[C_MEMBER_LO] | ((unsigned long long)(unsigned int)ctl[C_MEMBER_HI] << 32);
-                        running = true;
-                        ll_mbar_wait(bar, phase);
-                        phase ^= 1u;
-                    }
-                    else running = false, finished = true, n_act = 0;
-                }
-                __syncthreads(); // every thread of the team has read the control words before the leader rewrites them
-                if (need && running)
-                {
-                    n_act = min(a.S, a.n_layouts);
-                    for (int s = tt; s < a.S; s += a.TS)
-                    {
-                        if (s < n_act) slot_begin(a, env, sv, A0, s, s);
-                        else sv.active[s] = 0;
-                    }
-                    if (tt == 0) ctl[C_NEXT_LAYOUT] = n_act, ctl[C_N_ACTIVE] = n_act, ctl[C_DIRTY] = 0;
-                }
-                if (__syncthreads_and(finished)) break;
+                const int q = i >> 2, g = ctl->glist[q / E], s = g * E + q % E, mb = ctl->gmem[g];
+                if (sv.active[s])
+                    light_slot(a, s_layer[0], s_layer[n_layers - 1], env, sv, W0 + (size_t)mb * a.w_stride, ACT, ctl, res_fit, res_meta, mb, s, tid & 3,
+                               0xFu << (tid & 28));
             }
-            // ---- forward pass: one phase per layer
-            for (int l = 0; l < n_layers; ++l)
+            const int ev = __syncthreads_or(ctl->dirty != 0);
+            LL_PROF_MARK(0)
+            if (ev)
+            {
+                // ---- rare path: some episode ended without a successor
+                if (tid == 0) pool_manage<E>(a, env, ctl, sv, A0, W0, res_fit, res_meta);
+                __syncthreads();
+                if (ctl->exit_flag) break;
+                for (int mb = 0; mb < a.M; ++mb)
+                    if (ctl->status[mb] == ST_LOADING) ll_mbar_wait(&ctl->bar[mb], (uint32_t)ctl->parity[mb]);
+                for (int i = tid; i < ctl->n_init; i += threads) slot_begin(a, env, sv, A0, ctl->init_slot[i], ctl->init_layout[i]);
+                __syncthreads();
+                if (tid == 0)
+                    for (int mb = 0; mb < a.M; ++mb)
+                        if (ctl->status[mb] == ST_LOADING) ctl->status[mb] = ST_ACTIVE, ctl->parity[mb] ^= 1;
+                n_g = ctl->n_g;
+                // slots may have moved or (re)started: rebuild the first layer's activations of every live slot
+                for (int i = tid; i < n_g * E * 4; i += threads)
+                {
+                    const int q = i >> 2, g = ctl->glist[q / E], s = g * E + q % E;
+                    if (sv.active[s])
+                    {
+                        float st[5];
+#pragma unroll
+                        for (int k = 0; k < 5; ++k) st[k] = A0[k * a.S + s];
+                        first_layer_quad(a, s_layer[0], W0 + (size_t)ctl->gmem[g] * a.w_stride, ACT, st, s, tid & 3);
+                    }
+                }
+                __syncthreads();
+                LL_PROF_MARK(1)
+            }
+            // ---- forward pass: one phase per hidden-to-hidden layer (the first and the output layer belong to the light phase)
+            for (int l = 1; l < n_layers - 1; ++l)
             {
                 const fast_layer ly = s_layer[l];
-                if (running) layer_dispatch<E>(a, ly, W, ACT, tt, n_act);
+                layer_dispatch<E>(a, ly, ctl, W0, ACT, tid, n_g);
                 __syncthreads();
+                LL_PROF_MARK(4 + l)
             }
         }
+#undef LL_PROF_MARK
+        if (PROF && tid == 0 && a.prof)
+            for (int i = 0; i < 4 + n_layers; ++i) atomicAdd(&a.prof[i], (unsigned long long)pc[i]);
     }
 
     int pick_E(int L)
-    { // episode slots per thread: the candidate with the best slot utilisation, larger tiles on ties
+    { // slots per group (= episode rows of a register tile): the candidate with the best utilisation of a member's groups
         const int cand[5] = {8, 5, 4, 2, 1};
         int best = 1;
         double best_u = -1.0;
         for (int E : cand)
         {
-            int Ge = (L + E - 1) / E;
-            if (E * Ge > 64) Ge = 64 / E;
-            const int S = E * Ge, rounds = (L + S - 1) / S;
-            const double u = (double)L / ((double)rounds * S);
+            const int groups = (L + E - 1) / E;
+            const double u   = (double)L / ((double)groups * E);
             if (u > best_u + 1e-9) best_u = u, best = E;
         }
         return best;
+    }
+
+    int env_int(const char* name, int fallback)
+    {
+        const char* v = getenv(name);
+        return v && *v ? atoi(v) : fallback;
     }
 
     template <int E> int launch_fast_t(ll_ctx* ctx, const ll_episode_args& h)
@@ -463,76 +648,121 @@ namespace
         a.n_layouts = h.n_layouts, a.max_steps = h.max_steps, a.n_members = h.n_members;
         a.fitness = h.fitness, a.lr = h.lr, a.steps = h.steps, a.ep_steps = h.ep_steps, a.ep_fit = h.ep_fit, a.queue = h.queue;
         a.n_layers = tp.n_layers, a.act = tp.activation, a.p_dev = tp.p_dev;
-        const int L = h.n_layouts;
-        int Ge      = (L + E - 1) / E;
-        if (E * Ge > 64) Ge = 64 / E;
-        a.Ge = Ge, a.S = E * Ge;
+        const int L   = h.n_layouts;
         a.res_in_smem = L <= MAX_RES ? 1 : 0;
         if (!a.res_in_smem && !h.ep_steps) return ll_fail(ctx, LL_EINVAL, "fast episode kernel: more than 256 layouts need the per-episode buffers");
+        a.w_stride = (tp.p_dev + 31) & ~31;
 
-        int nog_max = 1;
-        for (int l = 0; l < tp.n_layers; ++l) nog_max = std::max(nog_max, tp.out_pad[l] / FO);
-        int TS = Ge * nog_max;
-        if (TS > MAX_THREADS) TS = MAX_THREADS;
-        TS   = TS >= 32 ? ((TS + 31) & ~31) : (TS <= 8 ? 8 : (TS <= 16 ? 16 : 32));
-        if (TS > MAX_THREADS) TS = MAX_THREADS;
-        a.TS = TS;
+        int max_smem = 0;
+        LL_CUDA(ctx, cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device));
+        int nog_max = 1, floats_per_slot = tp.out[tp.n_layers - 1], even_w = 0, odd_w = 0;
+        for (int l = 0; l < tp.n_layers; ++l)
+        {
+            nog_max = std::max(nog_max, tp.out_pad[l] / FO);
+            ((l & 1) ? odd_w : even_w) = std::max((l & 1) ? odd_w : even_w, tp.in[l]);
+        }
+        floats_per_slot += even_w + odd_w;
+        const int gpm         = (L + E - 1) / E; // groups one member can keep busy
+        const int group_bytes = E * (floats_per_slot * 4 + slot_view::bytes(1));
+        const int member_bytes = a.w_stride * 4 + (a.res_in_smem ? L * 12 : 0);
+        const int fixed_bytes  = (int)sizeof(pool_ctl) + 1024;
+        const int g_cap        = std::min(MAX_G, 384 / nog_max > 0 ? 384 / nog_max : 1);
+        // geometry: with `ctas` CTAs per SM, as many resident members as leave room for a pool of >= one member's groups
+        int M = 0, G = 0;
+        for (int ctas = 2; ctas >= 1 && M == 0; --ctas)
+        {
+            const int budget = max_smem / ctas - 1024;
+            for (int m = std::min<long long>(MAX_M, (long long)h.n_members); m >= 1; --m)
+            {
+                const int room = budget - fixed_bytes - m * member_bytes;
+                if (room < 0) continue;
+                int g = std::min({room / group_bytes, g_cap, m * gpm});
+                if (g >= std::min(gpm, g_cap) && (m >= 2 || ctas == 1))
+                {
+                    M = m, G = g;
+                    break;
+                }
+            }
+        }
+        if (M == 0) return ll_fail(ctx, LL_EINVAL, "fast episode kernel: topology does not fit in shared memory");
+        M = env_int("LL_FAST_M", M), G = env_int("LL_FAST_G", G); // tuning knobs for experiments
+        if (M < 1 || M > MAX_M || G < 1 || G > MAX_G) return ll_fail(ctx, LL_EINVAL, "fast episode kernel: bad LL_FAST_M / LL_FAST_G");
+        a.M = M, a.G = G, a.S = G * E;
+        int threads = std::min(384, G * nog_max);
+        threads     = std::max(32, (threads + 31) & ~31);
+        a.threads   = threads;
 
-        // activation buffers: even / odd ping-pong sized by the widest activation of each parity, then the output layer's Z
-        int even = 0, odd = 0;
-        for (int l = 0; l < tp.n_layers; ++l) ((l & 1) ? odd : even) = std::max((l & 1) ? odd : even, tp.in[l] * a.S);
+        const int even = even_w * a.S, odd = odd_w * a.S;
         for (int l = 0; l < tp.n_layers; ++l)
         {
             fast_layer& ly = a.layer[l];
             ly.in = tp.in[l], ly.out = tp.out[l], ly.out_pad = tp.out_pad[l], ly.w_off = tp.w_off[l], ly.b_off = tp.b_off[l];
-            ly.last  = l == tp.n_layers - 1;
-            ly.nog   = tp.out_pad[l] / FO;
-            ly.tiles = Ge * ly.nog;
-            int ks   = 1; // k-slices per tile: fill the team's threads, keep >= 8 rows per slice, slices of a tile in one warp
-            while (ks < 4 && (TS & 31) == 0 && ly.tiles * ks * 2 <= TS && ly.in / (ks * 2) >= 8) ks *= 2;
+            ly.last = l == tp.n_layers - 1;
+            ly.nog  = tp.out_pad[l] / FO;
+            int ks  = 1; // k-slices per tile: fill the CTA's threads, keep >= 8 rows per slice
+            while (ks < 4 && G * ly.nog * ks * 2 <= threads && ly.in / (ks * 2) >= 8) ks *= 2;
             ly.ks      = ks;
-            ly.klen    = (ly.in + ks - 1) / ks;
             ly.in_off  = (l & 1) ? even : 0;
             ly.out_off = ly.last ? even + odd : ((l & 1) ? 0 : even);
         }
         const int act_elems = even + odd + tp.out[tp.n_layers - 1] * a.S;
         auto up             = [](int v) { return (v + 127) & ~127; };
-        a.off_w             = 128;
-        a.off_act           = up(a.off_w + tp.p_dev * 4);
+        a.off_ctl           = 0;
+        a.off_w             = up((int)sizeof(pool_ctl));
+        a.off_act           = up(a.off_w + M * a.w_stride * 4);
         a.off_slot          = up(a.off_act + act_elems * 4);
         a.off_res           = up(a.off_slot + slot_view::bytes(a.S));
-        a.team_bytes        = up(a.off_res + (a.res_in_smem ? L * 12 : 0) + 16);
+        const size_t smem   = (size_t)up(a.off_res + (a.res_in_smem ? M * L * 12 : 0) + 16);
+        if (smem > (size_t)max_smem) return ll_fail(ctx, LL_EINVAL, "fast episode kernel: geometry needs " + std::to_string(smem) + " B of shared memory");
 
-        int max_smem = 0;
-        LL_CUDA(ctx, cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device));
-        if (a.team_bytes > max_smem) return ll_fail(ctx, LL_EINVAL, "fast episode kernel: a member team needs " + std::to_string(a.team_bytes) + " B of shared memory");
-        // teams per CTA: fill up to 256 threads, but keep at least two CTAs per SM when the topology allows it
-        int NT = std::max(1, MAX_THREADS / TS);
-        while (NT > 1 && (size_t)NT * a.team_bytes > (size_t)max_smem / 2) --NT;
-        const unsigned long long teams_needed = h.n_members;
-        if ((unsigned long long)NT > teams_needed) NT = (int)teams_needed;
-        a.NT              = NT;
-        const int threads = NT * TS;
-        const size_t smem = (size_t)NT * a.team_bytes;
-        auto kern         = ll_episode_fast_kernel<E>;
+        const bool prof = env_int("LL_FAST_PROF", 0) != 0;
+        auto kern       = prof ? ll_episode_fast_kernel<E, true> : ll_episode_fast_kernel<E, false>;
+        if (prof)
+        {
+            LL_CUDA(ctx, cudaMalloc(&a.prof, 64 * 8));
+            LL_CUDA(ctx, cudaMemsetAsync(a.prof, 0, 64 * 8, ctx->stream));
+        }
         LL_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int per_sm = 0;
         LL_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem));
         if (per_sm < 1) return ll_fail(ctx, LL_EINVAL, "fast episode kernel does not fit on an SM");
-        unsigned long long blocks_needed = (h.n_members + NT - 1) / NT;
-        unsigned int grid                = (unsigned int)std::min<unsigned long long>((unsigned long long)per_sm * ctx->sm_count, blocks_needed);
+        const unsigned long long blocks_needed = (h.n_members + M - 1) / M;
+        unsigned int grid = (unsigned int)std::min<unsigned long long>((unsigned long long)per_sm * ctx->sm_count, blocks_needed);
         if (grid < 1) grid = 1;
         ll_env<float> env;
         ll_make_env<float>(ctx->env_cfg, 1, &env);
         LL_CUDA(ctx, cudaMemsetAsync(h.queue, 0, sizeof(unsigned int), ctx->stream));
         kern<<<grid, threads, smem, ctx->stream>>>(env, a);
         LL_CUDA(ctx, cudaGetLastError());
+        if (prof)
+        {
+            unsigned long long pc[64];
+            LL_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            LL_CUDA(ctx, cudaMemcpy(pc, a.prof, sizeof(pc), cudaMemcpyDeviceToHost));
+            cudaFree(a.prof);
+            double tot = 0;
+            for (int i = 0; i < 4 + tp.n_layers; ++i)
+                if (i != 2 && i != 3) tot += (double)pc[i];
+            fprintf(stderr, "[ll_fast_prof] grid %u x %d thr, M %d G %d E %d smem %zu B, CTA-steps %llu, mean live groups %.2f, cycles/CTA-step %.0f |", grid,
+                    threads, M, G, E, smem, pc[2], pc[2] ? (double)pc[3] / pc[2] : 0.0, pc[2] ? tot / pc[2] : 0.0);
+            fprintf(stderr, " env %.1f%% manage %.1f%%", 100.0 * pc[0] / tot, 100.0 * pc[1] / tot);
+            for (int l = 0; l < tp.n_layers; ++l) fprintf(stderr, " L%d(ks%d) %.1f%%", l, a.layer[l].ks, 100.0 * pc[4 + l] / tot);
+            fprintf(stderr, "\n");
+        }
         return LL_OK;
     }
 } // namespace
 
-// Fast-mode launcher; returns LL_OK after enqueueing, or a negative value when the team kernel does not apply
-// (single-layout evaluations and traces stay on the lane-per-episode kernel of ll_episode.cu).
+// The pool kernel needs weight reuse across layouts (>= 4 of them) and the shape the light phase is written for: 5 inputs,
+// at least one hidden layer, at most 8 outputs (the reference's networks are 5-h...-4, src/nn_engine_trainer.cpp:45-48).
+bool ll_fast_applicable(const ll_ctx* ctx, int n_layouts)
+{
+    const ll_topo& tp = ctx->topo;
+    return n_layouts >= 4 && tp.n_layers >= 2 && tp.in[0] == 5 && tp.out[tp.n_layers - 1] <= FO;
+}
+
+// Fast-mode launcher (evaluations with >= 4 layouts; single-layout evaluations and traces stay on the lane-per-episode
+// kernel of ll_episode.cu, see ll_launch_episode).
 int ll_launch_episode_fast(ll_ctx* ctx, const ll_episode_args& a)
 {
     switch (pick_E(a.n_layouts))
