@@ -256,7 +256,9 @@ int ll_kernel_times_get(ll_ctx* ctx, ll_kernel_times* out, int reset);
  * all evaluations since the last reset, accumulated on the device so that timed loops need no per-generation read */
 int ll_step_counter(ll_ctx* ctx, double* total_steps, uint64_t* evaluations, int reset);
 /* FMA-pipe roofline denominator measured on this device: dependent-free FMA chains for ~`seconds`.
- * precision 32 -> FFMA, 322 -> packed FFMA2 (fma.rn.f32x2), 64 -> DFMA.  Result in TFLOP/s (2 flop per FMA). */
+ * precision 32 -> FFMA, 322 -> packed FFMA2 (fma.rn.f32x2), 64 -> DFMA; 19 -> mma.sync.m16n8k8 tf32 (191: at 16 warps
+ * per SM, 194: one warp per sub-partition, 195: one warp per sub-partition with a single dependent accumulator chain,
+ * 196/198: rotating operands at one/two warps per sub-partition, 197: m16n8k16 f16 with rotating operands), 16 -> mma.sync.m16n8k16 bf16 (warp-level tensor-core rate).  Result in TFLOP/s (2 flop per FMA). */
 int ll_microbench_fma(int32_t device, int32_t precision, double seconds, double* tflops, double* sm_mhz_est);
 /* HBM copy bandwidth (read+write bytes / time), GB/s */
 int ll_microbench_copy(int32_t device, uint64_t bytes, int32_t iters, double* gbps);

@@ -435,6 +435,7 @@ int ll_launch_episode(ll_ctx* ctx, const ll_episode_args& a)
     if (ctx->precision == 64) return launch_t<double, LL_MODE_EXACT>(ctx, a);
     if (ctx->mode == LL_MODE_FAST)
     { // the team kernel needs weight reuse across layouts; traces and tiny layout counts stay lane-per-episode
+        if (a.trace == nullptr && ll_mma_applicable(ctx, a.n_layouts)) return ll_launch_episode_mma(ctx, a);
         if (a.trace == nullptr && ll_fast_applicable(ctx, a.n_layouts)) return ll_launch_episode_fast(ctx, a);
         return launch_t<float, LL_MODE_FAST>(ctx, a);
     }
@@ -451,6 +452,7 @@ int ll_launch_feedforward(ll_ctx* ctx, const void* member_row, const void* d_sta
 const char* ll_episode_kernel_name(const ll_ctx* ctx, int n_layouts)
 {
     if (ctx->precision == 64) return "ll_episode_kernel<double,exact>";
+    if (ctx->mode == LL_MODE_FAST && ll_mma_applicable(ctx, n_layouts)) return "ll_episode_mma_kernel (3xTF32 mma.sync)";
     if (ctx->mode == LL_MODE_FAST) return ll_fast_applicable(ctx, n_layouts) ? "ll_episode_fast_kernel (slot-pool GEMM)" : "ll_episode_kernel<float,fast>";
     return "ll_episode_kernel<float,exact>";
 }
