@@ -1,28 +1,39 @@
-// ll_episode_mma.cu — K1 fast, tensor-core variant (fp32 via 3xTF32 mma.sync, LL_MODE_FAST, >= 9 layouts).
+// ll_episode_mma.cu — K1 fast, tensor-core variant (fp32 via 3 x fp16 split products on mma.sync, LL_MODE_FAST, >= 9 layouts).
 //
 // Replaces the same reference code as ll_episode.cu / ll_episode_fast.cu: train_generation / sim_task
 // src/nn_engine_trainer.cpp:443-539, GameLogicCpp<T> src/game_logic.cpp:124-388 and the ma-libs feedforward call
 // :501-502.  BASELINE.json north_star (a): "tensor cores (mma) are used only for the multi-start case, where each
 // individual's forward pass becomes a real small dense GEMM".
 //
-// Mapping.  All layouts of a member share its weights, so one forward pass over S concurrent episode
-// slots is D[S x out] = A[S x in] * W^T[in x out] per layer.  ONE WARP owns one member at a time and S = 16*MT slots:
-//   * the slots are the M dimension of mma.sync.m16n8k8 (tf32 operands, fp32 accumulate); the activations never leave
-//     the register file: the C fragment of layer l (rows g / g+8, columns 2t, 2t+1) IS the A fragment of layer l+1 once
-//     the k index of that layer is enumerated as (t -> 2t, t+4 -> 2t+1), which costs nothing because the B fragments
-//     (weights) are fetched as consecutive-k float2 pairs from shared memory in exactly that order;
-//   * the member's weights are staged once per member into shared memory as W[out][in] with an XOR swizzle of the 8-float
-//     k blocks that makes every LDS.64 fragment fetch bank-conflict free (no padding: 35.6 KB for 32_128_32, 6 members
-//     resident per SM);
-//   * fp32 accuracy on the tf32 tensor pipe: x = hi + lo with hi = x & 0xffffe000 (the 10-bit-mantissa part, exact) and
-//     lo = x - hi (exact), D += A_lo*B_hi + A_hi*B_lo + A_hi*B_hi — the dropped lo*lo term is < 2^-20 relative;
-//   * the lander of slot s lives in the registers of lane s; the argmax over the 4 outputs is two compares + one shuffle
-//     in the quad that holds them, the action and the next state travel between the fragment layout and the slot lanes
-//     by shuffles.  No barrier, no atomics and no shared-memory traffic other than the weight fetches in the step loop;
+// Mapping.  All layouts of a member share its weights, so one forward pass over 16 concurrent episode
+// slots is D[16 x out] = A[16 x in] * W^T[in x out] per layer.  ONE WARP owns one member at a time:
+//   * the 16 slots are the M dimension of mma.sync.m16n8k16 (f16 operands, fp32 accumulate).  The activations never leave
+//     the register file: the C fragment of layer l (rows g / g+8, columns 8nt+2t, 8nt+2t+1) packed to half2 IS register
+//     (nt & 1) * 2 + {0, 1} of the A fragment of k block nt / 2 of layer l+1;
+//   * fp32 accuracy from 11-bit operands: x = hi + lo with hi = the leading 11 significant bits and lo = x - hi (weights:
+//     lo scaled by 2^11 so that it stays in fp16's normal range); D = A_hi*B_hi + A_lo*B_hi + 2^-11 A_hi*B_lo', the
+//     dropped lo*lo term is < 2^-21 relative (measured: the share of episodes whose step count equals the exact fp32
+//     path's is the same 0.978 as for the FFMA kernel; dropping A_lo*B_hi as well lowers it to 0.50).  The three terms
+//     accumulate in three separate register tiles (a dependent HMMA would wait 21 cycles for its predecessor);
+//   * the member's weights are split ONCE per member, while they are staged into shared memory, and stored as ready-made
+//     B fragments {b0_hi, b1_hi, b0_lo, b1_lo} per (output block, k block, lane): one conflict-free LDS.128 per three
+//     HMMAs, 4 bytes per weight (35.3 KB for 32_128_32);
+//   * the lander of slot s lives in the registers of lane s (lanes 16..31 mirror 0..15); the argmax over the 4 outputs is
+//     two compares + one shuffle in the quad that holds them, the action and the next state travel between the
+//     fragment layout and the slot lanes by shuffles.  No barrier, no atomics and no shared-memory traffic other than
+//     the weight fetches in the step loop;
 //   * a slot whose episode ends takes the member's next layout (ballot + prefix count); the warp moves on to the next
 //     member of the global queue when all layouts are done.
+// Why these choices (measured on B200, ll_microbench_fma codes 19x/20xx): a legacy HMMA occupies its SM sub-partition's
+// issue port for its whole 8.56 cycles — other instructions do not issue in its shadow, from the same warp or another —
+// so the cost of a step is 8.56 * #HMMA + ~1.1 * #other instructions per sub-partition, and one warp per sub-partition
+// saturates it.  m16n8k16.f16 takes the same 8.56 cycles as m16n8k8.tf32 for twice the MACs, and pre-split weights
+// remove four ALU instructions per fragment: hence f16 splits instead of 3xTF32, and 4 or 8 warps per SM.
 // Layer sizes are template parameters (fragments are register arrays): the sample_runs topologies are instantiated,
-// anything else stays on the FFMA kernels.
+// anything else stays on the FFMA kernels.  fp16 range: weights beyond +-65504 saturate (such a pre-activation has
+// saturated tanh long before).
+#include <cuda_fp16.h>
+
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -41,30 +52,20 @@ namespace
             constexpr int a[NS] = {S...};
             return a[i];
         }
-        static __host__ __device__ constexpr int in8(int l) { return (sz(l) + 7) & ~7; }
+        static __host__ __device__ constexpr int in16(int l) { return (sz(l) + 15) & ~15; }
         static __host__ __device__ constexpr int out8(int l) { return (sz(l + 1) + 7) & ~7; }
-        // shared-memory (fragment-friendly) layout: per layer W[out8][in8] (swizzled) then b[out8]
+        // shared-memory layout in 32-bit words: per layer the B fragments [out8/8][in16/16][32 lanes][4 words], then the
+        // bias as accumulator fragments [out8/8][4 (t)][4] = {b[8nt+2t], b[8nt+2t+1], b[8nt+2t], b[8nt+2t+1]}
         static __host__ __device__ constexpr int w_off(int l)
         {
             int o = 0;
-            for (int i = 0; i < l; ++i) o += in8(i) * out8(i) + out8(i);
+            for (int i = 0; i < l; ++i) o += in16(i) * out8(i) + 2 * out8(i);
             return o;
         }
-        static __host__ __device__ constexpr int b_off(int l) { return w_off(l) + in8(l) * out8(l); }
+        static __host__ __device__ constexpr int b_off(int l) { return w_off(l) + in16(l) * out8(l); }
         static constexpr int total = w_off(NL);
-        static __host__ __device__ constexpr bool ok()
-        {
-            for (int l = 0; l < NL; ++l)
-            {
-                const int kb = in8(l) / 8;
-                if (!(kb == 1 || kb == 2 || kb % 4 == 0)) return false;
-            }
-            return sz(0) == 5 && sz(NL) <= 8;
-        }
+        static __host__ __device__ constexpr bool ok() { return sz(0) <= 8 && sz(NL) <= 8; }
     };
-
-    // XOR applied to the 8-float block index of row `o` so that rows o..o+3 land in four different 8-bank groups
-    template <int KB> __device__ __forceinline__ int swz(int o) { return KB >= 4 ? (o & 3) : (KB == 2 ? ((o >> 1) & 1) : 0); }
 
     struct mma_args
     {
@@ -80,167 +81,160 @@ namespace
         int w_off[LL_MAX_LAYERS], b_off[LL_MAX_LAYERS], out_pad[LL_MAX_LAYERS]; // the HBM row layout (ll_topo)
     };
 
-    __device__ __forceinline__ void mma_tf32(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1)
+    constexpr float LO_SCALE = 2048.f, LO_UNSCALE = 1.f / 2048.f;
+
+    __device__ __forceinline__ void mma_f16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1)
     {
-        asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-                     : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
-    }
-    __device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo)
-    {
-        hi = __float_as_uint(x) & 0xffffe000u;
-        lo = __float_as_uint(x - __uint_as_float(hi));
+                     : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
     }
 
-    // One layer for the warp's MT slot tiles.  a[mt][kt][4]: activations in C-fragment order ([0]=(g,2t) [1]=(g,2t+1)
-    // [2]=(g+8,2t) [3]=(g+8,2t+1) of k block kt); c[mt][nt][4]: act(bias + sum), same order, for output block nt.
-    //
-    // Accumulators.  A dependent HMMA (same accumulator) cannot issue until its predecessor has left the tensor pipe, and
-    // ptxas schedules the three HMMAs of one (kt, nt) tile next to each other (they share the freshly split B fragment).
-    // The three terms therefore accumulate into three separate register tiles — the dependent ones are then a whole k block
-    // apart — which are summed once per layer, small terms first.  Output blocks are processed in panels of PN <= 8 so that
-    // the 3 * PN * MT accumulator tiles fit the register file; the 4-output layer (one block) also alternates by k parity.
-    template <class N, int L, int MT, int EXP = 0>
-    __device__ __forceinline__ void layer_mma(const float* __restrict__ sw, int g, int t, const float (&a)[MT][N::in8(L) / 8][4],
-                                              float (&c)[MT][N::out8(L) / 8][4])
+    // Activations (x0, x1) -> half2 of the leading parts and half2 of the remainders.  hi = x & 0xffffe000 keeps 11
+    // significant bits (exact in fp16 over its normal range), lo = x - hi is exact in fp32 and below 2^-10 |x|.  The
+    // activations are bounded (tanh outputs, clamped state inputs <= 5), so lo needs no scaling: where it falls into the
+    // fp16 subnormal range its absolute error is <= 2^-25, the rounding noise of one fp32 product.
+    __device__ __forceinline__ void split_pair(float x0, float x1, uint32_t& hi, uint32_t& lo)
     {
-        constexpr int IN8 = N::in8(L), KT = IN8 / 8, NT = N::out8(L) / 8;
+        const float h0 = __uint_as_float(__float_as_uint(x0) & 0xffffe000u), h1 = __uint_as_float(__float_as_uint(x1) & 0xffffe000u);
+        const __half2 ph = __floats2half2_rn(h0, h1);
+        const __half2 pl = __floats2half2_rn(x0 - h0, x1 - h1);
+        hi = *reinterpret_cast<const uint32_t*>(&ph);
+        lo = *reinterpret_cast<const uint32_t*>(&pl);
+    }
+
+    // One layer for the warp's 16 slots.  ah/al[kt][4]: A fragments (hi / scaled lo) of k block kt (16 inputs).  Output:
+    // the next layer's A fragments nh/nl (tanh applied, split, packed), or for the output layer the raw fragment z[4]
+    // (rows g / g+8, outputs 2t, 2t+1) with tanh applied.  Output blocks go in panels of PN <= 8 so that the 3 * PN
+    // accumulator tiles stay in registers.
+    template <class N, int L>
+    __device__ __forceinline__ void layer_mma(const float* __restrict__ sw, int lane, int t, const uint32_t (&ah)[N::in16(L) / 16][4],
+                                              const uint32_t (&al)[N::in16(L) / 16][4],
+                                              uint32_t (&nh)[(N::out8(L) + 15) / 16][4], uint32_t (&nl)[(N::out8(L) + 15) / 16][4], float (&z)[4])
+    {
+        constexpr int KT = N::in16(L) / 16, NT = N::out8(L) / 8;
         constexpr int PN = NT >= 8 ? 8 : NT;
-        constexpr int KP = (PN * MT == 1 && KT >= 2) ? 2 : 1; // k-parity replicas
+        constexpr bool LAST = L == N::NL - 1;
         static_assert(NT % PN == 0, "output blocks must fill whole panels");
-        const float* W = sw + N::w_off(L) + g * IN8 + 2 * t;
-        const float* B = sw + N::b_off(L) + 2 * t;
-        int vr[4];
-        const int sx = swz<KT>(g);
+        const uint4* W = reinterpret_cast<const uint4*>(sw + N::w_off(L)) + lane;
+        const float4* B = reinterpret_cast<const float4*>(sw + N::b_off(L)) + t;
+        if constexpr (!LAST && (NT & 1))
+        { // odd number of output blocks: the upper half of the last k block of the next layer is padding
 #pragma unroll
-        for (int r = 0; r < 4; ++r) vr[r] = (r ^ sx) << 3;
+            for (int i = 2; i < 4; ++i) nh[NT / 2][i] = 0u, nl[NT / 2][i] = 0u;
+        }
 #pragma unroll
         for (int np = 0; np < NT; np += PN)
         {
-            float acc[KP][3][MT][PN][4]; // [.][0] A_lo*B_hi, [.][1] A_hi*B_lo, [.][2] bias + A_hi*B_hi
+            float acc[3][PN][4]; // [0] A_lo*B_hi, [1] A_hi*B_lo (scaled by 2^11), [2] bias + A_hi*B_hi
 #pragma unroll
             for (int j = 0; j < PN; ++j)
             {
-                const float2 b = *reinterpret_cast<const float2*>(B + (np + j) * 8);
+                const float4 b = B[(np + j) * 4]; // one LDS.128 straight into the accumulator tile
+                acc[2][j][0] = b.x, acc[2][j][1] = b.y, acc[2][j][2] = b.z, acc[2][j][3] = b.w;
 #pragma unroll
-                for (int mt = 0; mt < MT; ++mt)
-#pragma unroll
-                    for (int p = 0; p < KP; ++p)
-#pragma unroll
-                        for (int r = 0; r < 3; ++r)
-                        {
-                            const bool main = p == 0 && r == 2;
-                            acc[p][r][mt][j][0] = main ? b.x : 0.f, acc[p][r][mt][j][1] = main ? b.y : 0.f;
-                            acc[p][r][mt][j][2] = main ? b.x : 0.f, acc[p][r][mt][j][3] = main ? b.y : 0.f;
-                        }
+                for (int i = 0; i < 4; ++i) acc[0][j][i] = 0.f, acc[1][j][i] = 0.f;
             }
 #pragma unroll
             for (int kt = 0; kt < KT; ++kt)
-            {
-                uint32_t ah[MT][4], al[MT][4];
-#pragma unroll
-                for (int mt = 0; mt < MT; ++mt)
-#pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        if (EXP == 4 || EXP == 5) ah[mt][i] = __float_as_uint(a[mt][kt][i]), al[mt][i] = ah[mt][i] ^ 0x8000u;
-                        else split_tf32(a[mt][kt][i], ah[mt][i], al[mt][i]);
-                const int p = kt % KP;
 #pragma unroll
                 for (int j = 0; j < PN; ++j)
                 {
-                    float2 w;
-                    if (EXP == 2) w = make_float2(__int_as_float(vr[kt & 3] + j), __int_as_float(vr[(kt + 1) & 3] + np));
-                    else w = *reinterpret_cast<const float2*>(W + (np + j) * 8 * IN8 + (kt & ~3) * 8 + vr[kt & 3]);
-                    uint32_t bh0, bl0, bh1, bl1;
-                    if (EXP == 1 || EXP == 5) bh0 = __float_as_uint(w.x), bl0 = bh0 ^ 0x8000u, bh1 = __float_as_uint(w.y), bl1 = bh1 ^ 0x8000u;
-                    else split_tf32(w.x, bh0, bl0), split_tf32(w.y, bh1, bl1);
-                    // (Measured: dropping A_lo*B_hi halves the share of episodes whose step count equals the exact fp32
-                    // path's, 0.98 -> 0.50, so all three terms stay.)
+                    const uint4 w = W[((np + j) * KT + kt) * 32]; // {b0_hi, b1_hi, b0_lo, b1_lo}
+                    mma_f16(acc[0][j], al[kt], w.x, w.y);
+                    mma_f16(acc[1][j], ah[kt], w.z, w.w);
+                    mma_f16(acc[2][j], ah[kt], w.x, w.y);
+                }
 #pragma unroll
-                    for (int mt = 0; mt < MT; ++mt)
-                    {
-                        mma_tf32(acc[p][0][mt][j], al[mt][0], al[mt][2], al[mt][1], al[mt][3], bh0, bh1);
-                        mma_tf32(acc[p][1][mt][j], ah[mt][0], ah[mt][2], ah[mt][1], ah[mt][3], bl0, bl1);
-                        mma_tf32(acc[p][2][mt][j], ah[mt][0], ah[mt][2], ah[mt][1], ah[mt][3], bh0, bh1);
-                    }
+            for (int j = 0; j < PN; ++j)
+            {
+                float v[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) v[i] = ll_tanh_approx(fmaf(acc[1][j][i], LO_UNSCALE, acc[2][j][i] + acc[0][j][i]));
+                if constexpr (LAST)
+                {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) z[i] = v[i];
+                }
+                else
+                {
+                    const int nt = np + j;
+                    split_pair(v[0], v[1], nh[nt / 2][(nt & 1) * 2 + 0], nl[nt / 2][(nt & 1) * 2 + 0]); // row g
+                    split_pair(v[2], v[3], nh[nt / 2][(nt & 1) * 2 + 1], nl[nt / 2][(nt & 1) * 2 + 1]); // row g + 8
                 }
             }
-#pragma unroll
-            for (int mt = 0; mt < MT; ++mt)
-#pragma unroll
-                for (int j = 0; j < PN; ++j)
-#pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                    {
-                        float small = acc[0][0][mt][j][i] + acc[0][1][mt][j][i], big = acc[0][2][mt][j][i];
-                        if (KP == 2) small += acc[1][0][mt][j][i] + acc[1][1][mt][j][i], big += acc[1][2][mt][j][i];
-                        c[mt][np + j][i] = (EXP == 3 || EXP == 5) ? (big + small) * 0.01f : ll_tanh_approx(big + small);
-                    }
         }
     }
 
-    // layers L..NL-1; returns the output layer's fragments in `z`
-    template <class N, int L, int MT, int EXP = 0> struct chain
+    // layers L..NL-1; the output layer's fragment ends up in z
+    template <class N, int L> struct chain
     {
-        static __device__ __forceinline__ void run(const float* __restrict__ sw, int g, int t, const float (&a)[MT][N::in8(L) / 8][4],
-                                                   float (&z)[MT][4])
+        static __device__ __forceinline__ void run(const float* __restrict__ sw, int lane, int t, const uint32_t (&ah)[N::in16(L) / 16][4],
+                                                   const uint32_t (&al)[N::in16(L) / 16][4], float (&z)[4])
         {
-            float c[MT][N::out8(L) / 8][4];
-            layer_mma<N, L, MT, EXP>(sw, g, t, a, c);
-            if constexpr (L == N::NL - 1)
-            {
-#pragma unroll
-                for (int mt = 0; mt < MT; ++mt)
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) z[mt][i] = c[mt][0][i];
-            }
-            else chain<N, L + 1, MT, EXP>::run(sw, g, t, c, z);
+            uint32_t nh[(N::out8(L) + 15) / 16][4], nl[(N::out8(L) + 15) / 16][4];
+            layer_mma<N, L>(sw, lane, t, ah, al, nh, nl, z);
+            if constexpr (L + 1 < N::NL) chain<N, L + 1>::run(sw, lane, t, nh, nl, z);
         }
     };
 
-    // Stage one member row (HBM layout of ll_topo: per layer Wt[k][out_pad] then b[out_pad]) into the swizzled W[out][in]
-    // layout.  Coalesced 128-bit global reads, scattered 32-bit shared stores — once per member, i.e. once per
-    // ~10^5 forward passes, so a TMA copy plus a second shared buffer for the transposition would only cost residency.
+    // Stage one member row (HBM layout of ll_topo: per layer Wt[k][out_pad] then b[out_pad]) into the B-fragment layout,
+    // splitting every weight into its fp16 parts on the way.  Coalesced 128-bit global reads, scattered 16-bit shared
+    // stores — once per member, i.e. once per ~10^5 forward passes, so a TMA copy plus a second shared buffer for the
+    // re-layout would only cost residency.  Element (k, o) of a layer lives in lane (o & 7) * 4 + ((k & 7) >> 1) of the
+    // fragment of (output block o >> 3, k block k >> 4), word (k >> 3) & 1 (hi) / 2 + ((k >> 3) & 1) (lo), half k & 1.
     template <class N, int L> __device__ __forceinline__ void stage_layer(const mma_args& a, const float* __restrict__ row, float* __restrict__ sw, int lane)
     {
-        constexpr int IN = N::sz(L), IN8 = N::in8(L), OUT = N::sz(L + 1), OUT8 = N::out8(L), KB = IN8 / 8;
-        const int op = a.out_pad[L]; // == OUT8
+        constexpr int IN = N::sz(L), OUT = N::sz(L + 1), OUT8 = N::out8(L), KT = N::in16(L) / 16;
+        const int op      = a.out_pad[L]; // == OUT8
         const float4* src = reinterpret_cast<const float4*>(row + a.w_off[L]);
+        __half* dst       = reinterpret_cast<__half*>(sw + N::w_off(L));
         for (int i = lane; i < IN * OUT8 / 4; i += 32)
         {
             const float4 v = __ldg(src + i);
-            const int k = (i * 4) / op, o = (i * 4) - k * op;
-            float* d       = sw + N::w_off(L) + (k & 7);
+            const int k = (i * 4) / op, o0 = (i * 4) - k * op;
             const float e[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-            for (int j = 0; j < 4; ++j) d[(o + j) * IN8 + (((k >> 3) ^ swz<KB>(o + j)) << 3)] = (o + j < OUT) ? e[j] : 0.f;
+            for (int j = 0; j < 4; ++j)
+            {
+                const int o = o0 + j;
+                if (o < OUT)
+                {
+                    const __half hi = __float2half_rn(fminf(fmaxf(e[j], -65504.f), 65504.f));
+                    const __half lo = __float2half_rn(fminf(fmaxf((e[j] - __half2float(hi)) * LO_SCALE, -65504.f), 65504.f));
+                    const int word  = ((((o >> 3) * KT + (k >> 4)) * 32 + (o & 7) * 4 + ((k & 7) >> 1)) << 2) + ((k >> 3) & 1);
+                    dst[word * 2 + (k & 1)]       = hi;
+                    dst[(word + 2) * 2 + (k & 1)] = lo;
+                }
+            }
         }
-        for (int o = lane; o < OUT8; o += 32) sw[N::b_off(L) + o] = (o < OUT) ? __ldg(row + a.b_off[L] + o) : 0.f;
+        for (int i = lane; i < 2 * OUT8; i += 32)
+        { // word i of the bias fragments: block i >> 4, t = (i >> 2) & 3, element i & 3 -> output 8nt + 2t + (i & 1)
+            const int o           = (i >> 4) * 8 + ((i >> 2) & 3) * 2 + (i & 1);
+            sw[N::b_off(L) + i] = (o < OUT) ? __ldg(row + a.b_off[L] + o) : 0.f;
+        }
         if constexpr (L + 1 < N::NL) stage_layer<N, L + 1>(a, row, sw, lane);
     }
 
-    // warps per CTA (one CTA per SM, so that the warps spread evenly over the four SM sub-partitions): one member buffer
-    // each within 227 KB of shared memory, at most 12 (MT = 1) / 8 (MT = 2) so that every thread can keep its fragments in
-    // registers (65536 / (32 * warps) registers per thread)
-    template <class N, int MT> constexpr int max_warps()
+    // warps per CTA (one CTA per SM): one member buffer each within 227 KB of shared memory, a multiple of four so that the
+    // four sub-partitions carry the same load, at most 8 (one warp per sub-partition already saturates its issue port)
+    template <class N> constexpr int max_warps()
     {
-        const int by_smem = (227 * 1024) / (N::total * 4), cap = MT == 1 ? 12 : 8;
-        return by_smem < cap ? (by_smem < 1 ? 1 : by_smem) : cap;
+        const int by_smem = (227 * 1024) / (N::total * 4);
+        return by_smem >= 8 ? 8 : (by_smem >= 4 ? 4 : (by_smem < 1 ? 1 : by_smem));
     }
 
-    template <class N, int MT, int EXP = 0>
-    __global__ void __launch_bounds__(32 * max_warps<N, MT>(), 1) ll_episode_mma_kernel(const __grid_constant__ ll_env<float> env, const __grid_constant__ mma_args a)
+    template <class N, int EXP = 0>
+    __global__ void __launch_bounds__(32 * max_warps<N>(), 1) ll_episode_mma_kernel(const __grid_constant__ ll_env<float> env, const __grid_constant__ mma_args a)
     {
         static_assert(N::ok(), "topology not supported by the mma episode kernel");
         extern __shared__ __align__(16) float smem_all[];
         float* sw = smem_all + (threadIdx.x >> 5) * N::total; // this warp's weight buffer
-        constexpr int S   = 16 * MT;
-        const int lane    = threadIdx.x & 31;
-        const int g       = lane >> 2, t = lane & 3;
-        const int slot    = lane & (S - 1); // MT == 1: lanes 16..31 mirror lanes 0..15
-        const bool owner  = lane < S;
-        const unsigned sm = S == 32 ? 0xffffffffu : 0x0000ffffu;
-        const int L       = a.n_layouts;
+        const int lane   = threadIdx.x & 31;
+        const int g      = lane >> 2, t = lane & 3;
+        const int slot   = lane & 15; // lanes 16..31 mirror lanes 0..15
+        const bool owner = lane < 16;
+        const int L      = a.n_layouts;
 
         for (int i = lane; i < N::total; i += 32) sw[i] = 0.f; // k / out padding stays zero for the whole kernel
         __syncwarp();
@@ -263,7 +257,7 @@ namespace
             bool active = false;
             double fit_sum = 0.0;
             unsigned int steps_sum = 0, succ0 = 0, succ1 = 0;
-            int next_layout = L < S ? L : S;
+            int next_layout = L < 16 ? L : 16;
             if (slot < L)
             {
                 const ll_layout<float> lay = a.layouts[slot];
@@ -275,42 +269,40 @@ namespace
 
             while (__ballot_sync(0xffffffffu, active) != 0u)
             {
-                // ---- state -> A fragments of layer 0 (k block 0: positions (t, t+4) hold inputs (2t, 2t+1))
+                // ---- state -> A fragment of layer 0: registers 0 / 1 hold inputs (2t, 2t+1) of rows g / g+8, k >= 8 is padding
                 float st[5];
                 ll_get_state<float, LL_MODE_FAST>(env, p, cx, st, 1);
-                float a0[MT][1][4];
+                uint32_t a0h[1][4], a0l[1][4];
 #pragma unroll
-                for (int mt = 0; mt < MT; ++mt)
-#pragma unroll
-                    for (int h = 0; h < 2; ++h)
-                    {
-                        const int src = 16 * mt + 8 * h + g;
-                        const float v0 = __shfl_sync(0xffffffffu, st[0], src), v1 = __shfl_sync(0xffffffffu, st[1], src);
-                        const float v2 = __shfl_sync(0xffffffffu, st[2], src), v3 = __shfl_sync(0xffffffffu, st[3], src);
-                        const float v4 = __shfl_sync(0xffffffffu, st[4], src);
-                        a0[mt][0][2 * h + 0] = t == 0 ? v0 : (t == 1 ? v2 : (t == 2 ? v4 : 0.f));
-                        a0[mt][0][2 * h + 1] = t == 0 ? v1 : (t == 1 ? v3 : 0.f);
-                    }
+                for (int h = 0; h < 2; ++h)
+                {
+                    const int src = 8 * h + g;
+                    const float v0 = __shfl_sync(0xffffffffu, st[0], src), v1 = __shfl_sync(0xffffffffu, st[1], src);
+                    const float v2 = __shfl_sync(0xffffffffu, st[2], src), v3 = __shfl_sync(0xffffffffu, st[3], src);
+                    const float v4 = __shfl_sync(0xffffffffu, st[4], src);
+                    const float e0 = t == 0 ? v0 : (t == 1 ? v2 : (t == 2 ? v4 : 0.f));
+                    const float e1 = t == 0 ? v1 : (t == 1 ? v3 : 0.f);
+                    split_pair(e0, e1, a0h[0][h], a0l[0][h]);
+                    a0h[0][2 + h] = 0u, a0l[0][2 + h] = 0u;
+                }
                 // ---- forward pass, activations chained through registers
-                float z[MT][4];
-                chain<N, 0, MT, EXP>::run(sw, g, t, a0, z);
+                float z[4];
+                chain<N, 0>::run(sw, lane, t, a0h, a0l, z);
                 // ---- argmax over outputs 0..3 (first maximum wins): lanes t=0 hold outputs 0,1 and t=1 outputs 2,3
                 unsigned packed = 0;
 #pragma unroll
-                for (int mt = 0; mt < MT; ++mt)
-#pragma unroll
-                    for (int h = 0; h < 2; ++h)
-                    {
-                        float best = z[mt][2 * h];
-                        int idx    = 2 * t;
-                        if (z[mt][2 * h + 1] > best) best = z[mt][2 * h + 1], idx = 2 * t + 1;
-                        const float ob = __shfl_xor_sync(0xffffffffu, best, 1);
-                        const int oi   = __shfl_xor_sync(0xffffffffu, idx, 1);
-                        if (ob > best) idx = oi; // meaningful in lanes t == 0 (partner t == 1 holds outputs 2,3)
-                        packed |= (unsigned)idx << (8 * mt + 4 * h);
-                    }
+                for (int h = 0; h < 2; ++h)
+                {
+                    float best = z[2 * h];
+                    int idx    = 2 * t;
+                    if (z[2 * h + 1] > best) best = z[2 * h + 1], idx = 2 * t + 1;
+                    const float ob = __shfl_xor_sync(0xffffffffu, best, 1);
+                    const int oi   = __shfl_xor_sync(0xffffffffu, idx, 1);
+                    if (ob > best) idx = oi; // meaningful in lanes t == 0 (partner t == 1 holds outputs 2,3)
+                    packed |= (unsigned)idx << (4 * h);
+                }
                 const unsigned pk = __shfl_sync(0xffffffffu, packed, 4 * (slot & 7));
-                const int action  = (pk >> (8 * (slot >> 4) + 4 * ((slot >> 3) & 1))) & 15;
+                const int action  = (pk >> (4 * (slot >> 3))) & 15;
 
                 // ---- lander update + penalties (src/game_logic.cpp:295-320 through ll_env.cuh)
                 bool done = false, landed = false, success = false;
@@ -323,7 +315,7 @@ namespace
                     done = landed || steps >= a.max_steps;
                     if (EXP != 0) done = steps >= a.max_steps; // timing experiments: fixed-length episodes
                 }
-                const unsigned fin = __ballot_sync(0xffffffffu, done && owner) & sm;
+                const unsigned fin = __ballot_sync(0xffffffffu, done && owner) & 0xffffu;
                 if (fin)
                 { // some episode ended: book it, hand the slot the member's next layout
                     if (done)
@@ -382,7 +374,7 @@ namespace
         return v && *v ? atoi(v) : fallback;
     }
 
-    template <class N, int MT, int EXP = 0> int launch_mma_t(ll_ctx* ctx, const ll_episode_args& h)
+    template <class N, int EXP = 0> int launch_mma_t(ll_ctx* ctx, const ll_episode_args& h)
     {
         const ll_topo& tp = ctx->topo;
         mma_args a{};
@@ -391,10 +383,10 @@ namespace
         a.fitness = h.fitness, a.lr = h.lr, a.steps = h.steps, a.ep_steps = h.ep_steps, a.ep_fit = h.ep_fit, a.queue = h.queue;
         a.p_dev = tp.p_dev;
         for (int l = 0; l < tp.n_layers; ++l) a.w_off[l] = tp.w_off[l], a.b_off[l] = tp.b_off[l], a.out_pad[l] = tp.out_pad[l];
-        auto kern = ll_episode_mma_kernel<N, MT, EXP>;
+        auto kern = ll_episode_mma_kernel<N, EXP>;
         int max_smem = 0;
         LL_CUDA(ctx, cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device));
-        int warps = std::min<int>(max_warps<N, MT>(), max_smem / (N::total * 4));
+        int warps = std::min<int>(max_warps<N>(), max_smem / (N::total * 4));
         warps     = std::min(warps, env_int("LL_MMA_WARPS_PER_SM", warps));
         if (warps < 1) return ll_fail(ctx, LL_EINVAL, "mma episode kernel: the member row does not fit in shared memory");
         const size_t smem = (size_t)warps * N::total * 4;
@@ -407,11 +399,6 @@ namespace
         kern<<<grid, 32 * warps, smem, ctx->stream>>>(env, a);
         LL_CUDA(ctx, cudaGetLastError());
         return LL_OK;
-    }
-
-    template <class N> int launch_mma_n(ll_ctx* ctx, const ll_episode_args& h)
-    {
-        return env_int("LL_MMA_MT", 1) == 2 ? launch_mma_t<N, 2>(ctx, h) : launch_mma_t<N, 1>(ctx, h);
     }
 
     using net_16_16        = net_t<5, 16, 16, 4>;
@@ -447,24 +434,14 @@ bool ll_mma_applicable(const ll_ctx* ctx, int n_layouts)
 int ll_launch_episode_mma(ll_ctx* ctx, const ll_episode_args& a)
 {
     const ll_topo& tp = ctx->topo;
-#ifdef LL_MMA_EXPERIMENTS // timing-only variants with parts of the step removed (wrong results): where does the time go?
-    if (same_net<net_32_128_32>(tp))
-        switch (env_int("LL_MMA_EXP", 0))
-        {
-        case 1: return launch_mma_t<net_32_128_32, 1, 1>(ctx, a);
-        case 2: return launch_mma_t<net_32_128_32, 1, 2>(ctx, a);
-        case 3: return launch_mma_t<net_32_128_32, 1, 3>(ctx, a);
-        case 4: return launch_mma_t<net_32_128_32, 1, 4>(ctx, a);
-        case 5: return launch_mma_t<net_32_128_32, 1, 5>(ctx, a);
-        case 9: return launch_mma_t<net_32_128_32, 1, 9>(ctx, a);
-        default: break;
-        }
+#ifdef LL_MMA_EXPERIMENTS // timing-only variant with fixed-length episodes
+    if (same_net<net_32_128_32>(tp) && env_int("LL_MMA_EXP", 0) == 9) return launch_mma_t<net_32_128_32, 9>(ctx, a);
 #endif
-    if (same_net<net_32_128_32>(tp)) return launch_mma_n<net_32_128_32>(ctx, a);
-    if (same_net<net_16_64_32>(tp)) return launch_mma_n<net_16_64_32>(ctx, a);
-    if (same_net<net_8_16_32_16_8>(tp)) return launch_mma_n<net_8_16_32_16_8>(ctx, a);
-    if (same_net<net_8_16_8>(tp)) return launch_mma_n<net_8_16_8>(ctx, a);
-    if (same_net<net_16_32>(tp)) return launch_mma_n<net_16_32>(ctx, a);
-    if (same_net<net_16_16>(tp)) return launch_mma_n<net_16_16>(ctx, a);
+    if (same_net<net_32_128_32>(tp)) return launch_mma_t<net_32_128_32>(ctx, a);
+    if (same_net<net_16_64_32>(tp)) return launch_mma_t<net_16_64_32>(ctx, a);
+    if (same_net<net_8_16_32_16_8>(tp)) return launch_mma_t<net_8_16_32_16_8>(ctx, a);
+    if (same_net<net_8_16_8>(tp)) return launch_mma_t<net_8_16_8>(ctx, a);
+    if (same_net<net_16_32>(tp)) return launch_mma_t<net_16_32>(ctx, a);
+    if (same_net<net_16_16>(tp)) return launch_mma_t<net_16_16>(ctx, a);
     return ll_fail(ctx, LL_EINVAL, "mma episode kernel: topology not instantiated");
 }

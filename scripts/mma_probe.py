@@ -14,8 +14,8 @@ spad, lpad, d = util.layouts(50)
 spad, lpad, d = spad[:L], lpad[:L], d[:L]
 cfg = util.cfg_for(sizes)
 res = {}
-for name, envs in (("ffma", {"LL_FAST_KERNEL": "ffma"}), ("mma3", {"LL_FAST_KERNEL": "mma", "LL_MMA_TERMS": "3"}), ("mma2", {"LL_FAST_KERNEL": "mma", "LL_MMA_TERMS": "2"}),
-                   ("mma3_mt2", {"LL_FAST_KERNEL": "mma", "LL_MMA_TERMS": "3", "LL_MMA_MT": "2"})):
+for name, envs in (("ffma", {"LL_FAST_KERNEL": "ffma"}), ("mma", {"LL_FAST_KERNEL": "mma"}),
+                   ):
     for k in ("LL_FAST_KERNEL", "LL_MMA_TERMS", "LL_MMA_MT"):
         os.environ.pop(k, None)
     os.environ.update(envs)
