@@ -206,15 +206,24 @@ def measured_hbm_peak():
     return 6650.0, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
 
 
-def ncu_traffic(workload):
-    """DRAM bytes per launch of the episode kernel from the committed ncu --set full capture, if there is one."""
+def ncu_traffic(workload, members):
+    """DRAM bytes per launch of the episode kernel from the committed ncu --set full capture (bytes per member of the
+    captured launch x the members of this launch: the kernel reads every member row exactly once), if there is one."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(p):
         try:
-            return json.load(open(p)).get(workload)
+            e = json.load(open(p)).get(workload)
+            return float(e["bytes_per_member"]) * members if e else None
         except Exception:
             return None
     return None
+
+
+# HMMA work the tensor-core episode kernel really issues per lander step (ll_episode_mma.cu): per layer
+# ceil(in/16) * ceil(out/8) tiles x 3 split products x 16*8*16 MACs, for a 16-slot tile
+def hmma_flop_per_step(sizes):
+    tiles = sum(((sizes[i] + 15) // 16) * ((sizes[i + 1] + 7) // 8) for i in range(len(sizes) - 1))
+    return tiles * 3 * 2 * 16 * 8 * 16 / 16.0
 
 
 def run_gpu(args):
@@ -255,6 +264,9 @@ def run_gpu(args):
     pcode = 64 if precision == 64 else 32
     _abi.check(_abi.lib.ll_microbench_fma(local_rank, pcode, 0.25, C.byref(fma_burst), C.byref(mhz_b)))
     _abi.check(_abi.lib.ll_microbench_fma(local_rank, pcode, 3.0, C.byref(fma_sust), C.byref(mhz_s)))
+    hmma_peak, mhz_h = C.c_double(), C.c_double()
+    if precision == 32 and mode == 1:  # warp-level f16 HMMA rate (m16n8k16, rotating operands), the tensor-core kernel's pipe
+        _abi.check(_abi.lib.ll_microbench_fma(local_rank, 197, 0.25, C.byref(hmma_peak), C.byref(mhz_h)))
 
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
@@ -388,7 +400,8 @@ def run_gpu(args):
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "fp64_fma" if precision == 64 else "fp32_fma", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                         "frac": achieved / peak if peak > 0 else None, "traffic": ncu_traffic(args.workload),
+                         "frac": achieved / peak if peak > 0 else None,
+                         "traffic": ncu_traffic(args.workload, eng.pop_local) if "mma" in eng.info.kernel.decode() else None,
                          "kernel": eng.info.kernel.decode(), "flop_per_lander_step": fps,
                          "kernel_ms_per_launch": episode_ms_max / max(1, args.steps),
                          "kernel_share_of_step": episode_ms_max / ms_total_max if ms_total_max > 0 else None,
@@ -397,6 +410,12 @@ def run_gpu(args):
                          "peak_burst": fma_burst.value, "peak_sustained": fma_sust.value,
                          "sm_mhz_during_peak": mhz_s.value if long_kernel else mhz_b.value,
                          "peak_nominal_1965mhz": (148 * 128 * 2 * 1.965e9 / 1e12) if precision == 32 else None},
+            "tensor_pipe": ({"note": "explains the FMA-roofline fraction: HMMA flop the kernel issues (3 f16-split products, padded "
+                                     "tiles, every row of the 16-slot tile whether its episode is live or not counted as live) "
+                                     "against the measured mma.sync.m16n8k16.f16 rate",
+                             "hmma_flop_per_lander_step": hmma_flop_per_step(sizes),
+                             "achieved_live_rows": steps_local * hmma_flop_per_step(sizes) / (episode_ms_max * 1e-3) / 1e12 if episode_ms_max > 0 else None,
+                             "peak": hmma_peak.value, "unit": "TFLOP/s"} if "mma" in eng.info.kernel.decode() else None),
             "roofline_ga": {"bound": "hbm", "achieved": ga_gbs, "peak": hbm_peak, "unit": "GB/s",
                             "frac": ga_gbs / hbm_peak if hbm_peak else None, "traffic": None, "kernel": "ll_create_population_kernel",
                             "kernel_ms_per_launch": kt.mutate_ms / max(1, kt.mutate_launches), "peak_source": hbm_src},

@@ -488,6 +488,19 @@ extern "C" int ll_set_layouts(ll_ctx* ctx, const int32_t* spad_x1, const int32_t
         if (ctx->precision == 64) ll_make_layout<double>(ctx->env_cfg, spad_x1[i], lpad_x1[i], (int)directions[i], static_cast<ll_layout<double>*>(ctx->h_pin) + i);
         else ll_make_layout<float>(ctx->env_cfg, spad_x1[i], lpad_x1[i], (int)directions[i], static_cast<ll_layout<float>*>(ctx->h_pin) + i);
     }
+    {
+        // schedule hint for the slot-refilling kernels: entry i names the layout to start i-th, longest expected flight
+        // (horizontal distance between the pads) first — a member's episodes are then packed onto its slots LPT-style
+        std::vector<int> order((size_t)n);
+        std::vector<double> dist((size_t)n);
+        for (int i = 0; i < n; ++i) order[(size_t)i] = i, dist[(size_t)i] = std::abs((double)spad_x1[i] - (double)lpad_x1[i]);
+        std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return dist[(size_t)x] > dist[(size_t)y]; });
+        for (int i = 0; i < n; ++i)
+        {
+            if (ctx->precision == 64) static_cast<ll_layout<double>*>(ctx->h_pin)[i].next = order[(size_t)i];
+            else static_cast<ll_layout<float>*>(ctx->h_pin)[i].next = order[(size_t)i];
+        }
+    }
     LL_CUDA(ctx, cudaMemcpyAsync(ctx->d_layouts, ctx->h_pin, lay_bytes * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
     LL_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->n_layouts = n;

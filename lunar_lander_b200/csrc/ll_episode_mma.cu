@@ -260,8 +260,9 @@ namespace
             int next_layout = L < 16 ? L : 16;
             if (slot < L)
             {
-                const ll_layout<float> lay = a.layouts[slot];
-                layout = slot, dir = lay.dir;
+                layout                     = a.layouts[slot].next; // start order: longest expected flight first
+                const ll_layout<float> lay = a.layouts[layout];
+                dir                        = lay.dir;
                 cx = lay.center_x, lpad = lay.lpad_x1, lpad_r = lay.lpad_right;
                 p      = ll_lander<float>{lay.init_x, env.y0, env.vx0, env.vy0, env.max_fuel};
                 active = true;
@@ -333,8 +334,9 @@ namespace
                         const int nl = next_layout + __popc(fin & ((1u << slot) - 1u));
                         if (nl < L)
                         { // reset(spad_x1, lpad_x1): src/game_logic.cpp:143-154
-                            const ll_layout<float> lay = a.layouts[nl];
-                            layout = nl, dir = lay.dir;
+                            layout                     = a.layouts[nl].next;
+                            const ll_layout<float> lay = a.layouts[layout];
+                            dir                        = lay.dir;
                             cx = lay.center_x, lpad = lay.lpad_x1, lpad_r = lay.lpad_right;
                             p     = ll_lander<float>{lay.init_x, env.y0, env.vx0, env.vy0, env.max_fuel};
                             steps = 0, acc = 0.0;

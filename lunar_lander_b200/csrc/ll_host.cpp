@@ -86,7 +86,7 @@ template <typename T> void ll_make_layout(const ll_env_cfg& c, int spad_x1, int 
     out->lpad_right = lpad + lpad_w;
     out->center_x   = (width > T(0) && height > T(0)) ? lpad + lpad_w / T(2.0) : T(0);
     out->dir        = dir;
-    out->pad_       = 0;
+    out->next       = 0;
 }
 template void ll_make_layout<float>(const ll_env_cfg&, int, int, int, ll_layout<float>*);
 template void ll_make_layout<double>(const ll_env_cfg&, int, int, int, ll_layout<double>*);

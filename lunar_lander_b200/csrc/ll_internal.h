@@ -49,7 +49,8 @@ template <typename T> struct ll_env
 template <typename T> struct ll_layout
 {
     T init_x, lpad_x1, lpad_right, center_x;
-    int dir, pad_;
+    int dir;
+    int next; // schedule hint (ll_set_layouts): entry i holds the index of the layout to START i-th, longest expected flight first
 };
 
 struct ll_select_state

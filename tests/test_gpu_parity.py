@@ -330,6 +330,45 @@ def test_fast_mode_outcomes(ll, po, topo, n_layouts, pop):
     eng.close()
 
 
+@pytest.mark.parametrize("topo,n_layouts,pop", [("32_128_32", 50, 128), ("8_16_32_16_8", 50, 128), ("16_16", 17, 256), ("16_64_32", 9, 192)])
+def test_fast_tensor_core_kernel_tracks_exact_fp32(ll, po, topo, n_layouts, pop, monkeypatch):
+    """The tensor-core episode kernel (fp32 from three fp16-split products, ll_episode_mma.cu) against the FFMA fast kernel
+    and the exact fp32 oracle on the same members: a chaotic controller amplifies any rounding difference, so the measure
+    is the share of episodes that end at the same step with the same outcome.  Bars (measured 0.97-0.98 for BOTH fast
+    kernels, 0.997 between them; a fragment-layout or split error drops them below 0.6): >= 0.95 against the oracle,
+    >= 0.98 between the two fast kernels, outcome flags >= 0.99."""
+    members, sizes = util.elite_population(topo, pop, 4, noise=0.02)
+    members[pop // 2:] += util.random_population(sizes, pop - pop // 2, 8, scale=0.05)
+    spad, lpad, d = util.layouts(50)
+    spad, lpad, d = spad[:n_layouts], lpad[:n_layouts], d[:n_layouts]
+    got = {}
+    for kern in ("mma", "ffma"):
+        monkeypatch.setenv("LL_FAST_KERNEL", kern)
+        eng, cfg = _engine(ll, sizes, pop, 32, mode=1)
+        eng.set_members(0, members)
+        fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
+        name = eng.info.kernel.decode()
+        assert ("mma" in name) == (kern == "mma"), name
+        ep_steps, flags, ep_fit = eng.read_episodes()
+        assert np.array_equal(steps, ep_steps.sum(axis=1).astype(np.float64))
+        got[kern] = (ep_steps, flags, fit, lr)
+        eng.close()
+    want = po.evaluate(cfg.env_cfg(), sizes, 1, members.astype(np.float32), spad, lpad, d, 5000, 32, threads=8)
+    for kern, (ep_steps, flags, fit, lr) in got.items():
+        assert np.mean(ep_steps == want["ep_steps"]) >= 0.95, kern
+        assert np.mean(flags == want["ep_flags"]) >= 0.99, kern
+        assert np.mean(lr == want["lr"]) >= 0.9, kern
+    assert np.mean(got["mma"][0] == got["ffma"][0]) >= 0.98
+    same = got["mma"][0] == want["ep_steps"]
+    # members whose episodes all end at the oracle's step: their fitness differs only by the rounding of the states the
+    # step penalties are taken from
+    ef = got["mma"][2]
+    rows = same.all(axis=1)
+    assert rows.mean() >= 0.2
+    rel = np.abs(ef[rows] - want["fitness"][rows]) / np.maximum(1.0, np.abs(want["fitness"][rows]))
+    assert np.median(rel) <= 1e-5 and np.percentile(rel, 75) <= 1e-3, (np.median(rel), np.percentile(rel, 75), rel.max())
+
+
 def test_fast_mode_constant_policies(ll):
     """Constant-action networks do not depend on the forward arithmetic: the fast kernel must reproduce the reference-owned
     known answers of the environment in step counts and flags, fitness to float rounding."""
