@@ -26,7 +26,7 @@ namespace
         unsigned long long first_global, pop_global, pop_local;
         unsigned int seed, gen, top;
         unsigned long long first_child;  // global slots below this are elite copies
-        unsigned long long first_inject; // global slots >= this are fresh random individuals
+        unsigned long long n_children, n_inject; // ll_is_injected(slot - first_child, ...) marks the fresh random individuals
         int from_elites;
         int p_canon, p_dev;
         double sigma_init, sigma_mut;
@@ -61,7 +61,7 @@ namespace
                 if (2 * p + 1 < a.p_canon) g[2 * p + 1] = (T)n1;
             }
             __syncthreads();
-            const bool inject = !a.from_elites || mg >= a.first_inject;
+            const bool inject = !a.from_elites || ll_is_injected(mg - a.first_child, a.n_children, a.n_inject);
             const T s_init = (T)a.sigma_init, s_mut = (T)a.sigma_mut;
             const T* parent = nullptr;
             if (!inject) parent = static_cast<const T*>(a.elites) + (size_t)ll_parent_pick(a.seed, a.gen, (uint32_t)mg, a.top) * a.p_dev;
@@ -310,7 +310,7 @@ int ll_launch_create_population_gen(ll_ctx* ctx, int elitism, uint64_t gen)
     a.from_elites = ctx->has_elites ? 1 : 0;
     if (!ctx->has_elites)
     { // first population: every slot is a fresh Gaussian individual
-        a.gen = (unsigned int)gen, a.first_child = 0, a.first_inject = 0;
+        a.gen = (unsigned int)gen, a.first_child = 0, a.n_children = ctx->pop_global, a.n_inject = ctx->pop_global;
     }
     else
     {
@@ -324,7 +324,7 @@ int ll_launch_create_population_gen(ll_ctx* ctx, int elitism, uint64_t gen)
             n_inject       = v <= 0.0 ? 0ull : (unsigned long long)v; // floor(x + 0.5) for x >= 0
         }
         if (n_inject > n_children) n_inject = n_children;
-        a.first_inject = ctx->pop_global - n_inject;
+        a.n_children = n_children, a.n_inject = n_inject;
     }
     const size_t smem = ((size_t)ctx->topo.p_canon + 1) * ctx->elt;
     unsigned int grid = (unsigned int)(ctx->pop_local < (1u << 20) ? ctx->pop_local : (1u << 20));

@@ -91,4 +91,14 @@ LL_HD uint32_t ll_parent_pick(uint32_t seed, uint32_t gen, uint32_t member, uint
     return (uint32_t)(((uint64_t)w.v[0] * (uint64_t)top) >> 32);
 }
 
+// Which child slots are fresh random individuals (MIXED_WITH_RANDOM_INJECTION): n_inject of the n_children slots, spread
+// evenly (child c is fresh iff the running count floor((c + 1) n_inject / n_children) steps at c) instead of bunched at
+// the end, so every contiguous shard of the population carries the same mix of long-lived elite children and short-lived
+// random individuals (2 GPUs: 1.36 s vs 1.02 s per generation for the shard that held all the elite children).
+LL_HD bool ll_is_injected(uint64_t child, uint64_t n_children, uint64_t n_inject)
+{
+    if (n_inject >= n_children) return true;
+    return ((child + 1) * n_inject) / n_children != (child * n_inject) / n_children;
+}
+
 #endif // LL_PHILOX_H_

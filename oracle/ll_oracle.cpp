@@ -303,7 +303,7 @@ namespace
         const T s_init = static_cast<T>(sigma_init), s_mut = static_cast<T>(sigma_mut);
         for (uint64_t i = first; i < pop; ++i)
         {
-            const bool inject = i >= pop - n_inject;
+            const bool inject = ll_is_injected(i - first, pop - first, n_inject);
             const T* parent   = inject ? nullptr : &elites[(size_t)ll_parent_pick(seed, gen, (uint32_t)i, (uint32_t)top) * P];
             T* dst            = params + i * P;
             for (size_t j = 0; j < P; j += 2)

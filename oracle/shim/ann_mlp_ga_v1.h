@@ -270,7 +270,7 @@ namespace nn
             }
         }
 
-        // slots [first, pop): the last n_inject of them are fresh N(0, sigma_init^2) individuals, the
+        // slots [first, pop): n_inject of them, spread evenly (ll_is_injected), are fresh N(0, sigma_init^2) individuals, the
         // others are  elite[pick] + sigma_mut * N(0,1)  with pick = ll_parent_pick(seed, gen, slot, top).
         void regenerate(uint32_t gen, size_t first, bool from_elites)
         {
@@ -288,7 +288,7 @@ namespace nn
             const T s_init = static_cast<T>(sigma_init), s_mut = static_cast<T>(sigma_mut);
             for (size_t i = first; i < pop_; ++i)
             {
-                const bool inject = i >= pop_ - n_inject;
+                const bool inject = ll_is_injected(i - first, n_children, n_inject);
                 const T* parent   = nullptr;
                 if (!inject)
                     parent = &elites[ll_parent_pick(seed_, gen, static_cast<uint32_t>(i), static_cast<uint32_t>(top_)) * P_];

@@ -176,8 +176,7 @@ def test_create_population_bit_exact(ll, po, precision):
     want1 = po.create_population(sizes, 5247, pop, top, 7, 2, 0.35, True, True, 1.0, 0.1, got0, precision)
     assert np.array_equal(got1, want1)
     assert np.array_equal(got1[:top], got0[:top])  # elitism
-    n_inject = int(np.floor(0.35 * (pop - top) + 0.5))
-    assert abs(got1[pop - n_inject:].std() - 1.0) < 0.03
+    assert abs(got1[util.injected_mask(pop, top, 0.35)].std() - 1.0) < 0.03
     # no elitism, all-from-elites strategy
     eng.set_population_strategy(1, 0.0)
     eng.create_population(False)

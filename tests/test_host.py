@@ -187,10 +187,11 @@ def test_create_population_statistics(built):
     assert abs(p0.mean()) < 0.01 and abs(p0.std() - 1.0) < 0.01
     p1 = po.create_population(sizes, 5247, pop, top, 1, 2, 0.35, True, True, 1.0, 0.1, p0)
     assert np.array_equal(p1[:top], p0[:top])
-    n_inject = int(np.floor(0.35 * (pop - top) + 0.5))
-    kids = p1[top:pop - n_inject]
+    fresh = util.injected_mask(pop, top, 0.35)  # spread evenly over the child slots: any contiguous shard gets the same mix
+    assert fresh[top:top + 100].sum() in (34, 35, 36)
+    kids = p1[top:][~fresh[top:]]
     d = np.abs(kids[:, None, :] - p0[None, :top, :]).mean(axis=2).min(axis=1)  # distance to the nearest elite
-    assert d.max() < 0.15 and abs(p1[pop - n_inject:].std() - 1.0) < 0.02
+    assert d.max() < 0.15 and abs(p1[fresh].std() - 1.0) < 0.02
     # generation / seed / member all change the draw; the same key reproduces it
     assert not np.array_equal(p1, po.create_population(sizes, 5247, pop, top, 2, 2, 0.35, True, True, 1.0, 0.1, p0))
     assert np.array_equal(p1, po.create_population(sizes, 5247, pop, top, 1, 2, 0.35, True, True, 1.0, 0.1, p0))

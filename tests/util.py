@@ -60,3 +60,15 @@ def cfg_for(topo_sizes, **overrides):
     ov = {"NNConfig.hlayers": ",".join(str(s) for s in topo_sizes[1:-1])}
     ov.update(overrides)
     return ll.Config(CFG_PATH, ov)
+
+
+def injected_mask(pop, top, ratio):
+    """Child slots that hold fresh random individuals (ll_is_injected, csrc/ll_philox.h): n_inject of the pop - top children,
+    spread evenly over the child slots."""
+    n_children = pop - top
+    n_inject = min(n_children, int(np.floor(ratio * n_children + 0.5)))
+    c = np.arange(n_children, dtype=np.int64)
+    m = np.zeros(pop, dtype=bool)
+    m[top:] = ((c + 1) * n_inject) // n_children != (c * n_inject) // n_children
+    assert m.sum() == n_inject
+    return m
