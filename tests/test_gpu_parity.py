@@ -304,17 +304,21 @@ def test_weight_file_roundtrip(ll, po, tmp_path):
 # 7. fast fp32 mode: judged on outcomes, not sequences
 @pytest.mark.parametrize("topo,n_layouts,pop", [("16_64_32", 50, 256), ("32_128_32", 50, 96), ("16_64_32", 8, 512), ("8_16_8", 33, 300),
                                                 ("16_16", 5, 777), ("8_16_32_16_8", 50, 64), ("16_16", 1, 2048)])
-def test_fast_mode_outcomes(ll, po, topo, n_layouts, pop):
-    """LL_MODE_FAST (team-GEMM kernel for >= 4 layouts, lane-per-episode kernel below): FMA, free summation order and
+@pytest.mark.parametrize("kernel", ["mma", "ffma"])
+def test_fast_mode_outcomes(ll, po, topo, n_layouts, pop, kernel, monkeypatch):
+    """LL_MODE_FAST, tensor-core kernel (default for the sample_runs topologies) and the FFMA kernels (LL_FAST_KERNEL=ffma:
+    slot-pool GEMM kernel for >= 4 layouts, lane-per-episode kernel below; what other topologies run on): FMA, free summation order and
     tanh.approx.f32 change individual trajectories, so the bar is statistical — stated here: landed-successfully rate
     within 2 points, total lander steps within 2 %, mean fitness within 3 % of the mean |fitness| of the exact fp32 path."""
     members, sizes = util.elite_population(topo, pop, 4, noise=0.02)
     members[pop // 2:] += util.random_population(sizes, pop - pop // 2, 8, scale=0.05)  # a more diverse half
     spad, lpad, d = util.layouts(50)
     spad, lpad, d = spad[:n_layouts], lpad[:n_layouts], d[:n_layouts]
+    monkeypatch.setenv("LL_FAST_KERNEL", kernel)
     eng, cfg = _engine(ll, sizes, pop, 32, mode=1)
     eng.set_members(0, members)
     fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
+    assert ("mma" in eng.info.kernel.decode()) == (kernel == "mma")
     ep_steps, flags, ep_fit = eng.read_episodes()
     want = po.evaluate(cfg.env_cfg(), sizes, 1, members.astype(np.float32), spad, lpad, d, 5000, 32, threads=8)
     assert np.array_equal(steps, ep_steps.sum(axis=1).astype(np.float64))
