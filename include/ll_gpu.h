@@ -139,6 +139,15 @@ typedef struct ll_kernel_times
     uint64_t other_launches;                        /* layout transposes, trace, feedforward */
 } ll_kernel_times;
 
+/* The public face of one GameLogicCpp<T> object (src/game_logic.h:17-21 members + is_done() + get_state()). */
+typedef struct ll_sim_view
+{
+    double x, y, vx, vy, fuel;
+    double landing_pad_center_x, landing_pad_y;
+    int32_t landed, crashed, landed_successfully, time_step, last_action, done;
+    double state[5]; /* get_state() of the current state */
+} ll_sim_view;
+
 typedef struct ll_ctx ll_ctx;
 
 int ll_abi_version(void);
@@ -248,6 +257,25 @@ int ll_generate_random_pad_positions(double screen_width, int32_t spad_width, in
 int ll_balance_layouts(int32_t* spad_x1, int32_t* lpad_x1, double* spad_center, double* lpad_center,
                        uint64_t* directions, int32_t n, double target_ltr_ratio, double screen_width,
                        double spad_width, double lpad_width);
+
+/* ---- one stepped lander: the GameLogicCpp<T> object of nn_play / play mode ----------------------------------------
+ * replaces  GameLogicCpp<T>::reset() / reset(T spad_x1, T lpad_x1)     src/game_logic.cpp:124-154
+ *           update(int action, T* state, size_t n) -> done             src/game_logic.cpp:295-310
+ *           get_state / is_done / the public members                   src/game_logic.cpp:253-293, src/game_logic.h:17-21
+ *           calculate_step_penalty(action)                             src/game_logic.cpp:312-320
+ *           calculate_terminal_penalty(steps) / (steps, dir, bonus&)   src/game_logic.cpp:322-388
+ *      and  the lunar_lander_cpp bindings of those                     src/lunar_lander_cpp.cpp:21-93
+ * The lander lives on the device and is advanced by the same device functions as the episode kernel, in the
+ * context's precision with the exact arithmetic.  `out` (may be NULL) receives the state after the call. */
+int ll_sim_reset(ll_ctx* ctx, int32_t use_pads, double spad_x1, double lpad_x1, ll_sim_view* out);
+int ll_sim_update(ll_ctx* ctx, int32_t action, ll_sim_view* out); /* out->done = the reference's return value */
+int ll_sim_get(ll_ctx* ctx, ll_sim_view* out);
+/* writes x, y, vx, vy, fuel, landing_pad_center_x, the three flags and last_action (the def_readwrite members) */
+int ll_sim_set(ll_ctx* ctx, const ll_sim_view* in, ll_sim_view* out);
+int ll_sim_step_penalty(ll_ctx* ctx, int32_t action, double* penalty);
+/* direction < 0: the one-argument overload; 0/1: the three-argument one, bonus_lr[direction] += tp_landed_lr_bonus on a
+ * successful landing (bonus_lr: 2 doubles, in/out, may be NULL) */
+int ll_sim_terminal_penalty(ll_ctx* ctx, int32_t steps_taken, int32_t direction, double* penalty, double* bonus_lr);
 
 /* ---- measurement ---------------------------------------------------------------------------------------------*/
 int ll_profile(ll_ctx* ctx, int enable);                 /* CUDA-event timing of every kernel class */

@@ -70,6 +70,13 @@ class KernelTimes(C.Structure):
                 ("mutate_ms", C.c_double), ("mutate_launches", C.c_uint64), ("other_launches", C.c_uint64)]
 
 
+class SimView(C.Structure):
+    _fields_ = [("x", C.c_double), ("y", C.c_double), ("vx", C.c_double), ("vy", C.c_double), ("fuel", C.c_double),
+                ("landing_pad_center_x", C.c_double), ("landing_pad_y", C.c_double), ("landed", C.c_int32),
+                ("crashed", C.c_int32), ("landed_successfully", C.c_int32), ("time_step", C.c_int32),
+                ("last_action", C.c_int32), ("done", C.c_int32), ("state", C.c_double * 5)]
+
+
 _ctx = C.c_void_p
 _i32p, _u64p, _f64p = C.POINTER(C.c_int32), C.POINTER(C.c_uint64), C.POINTER(C.c_double)
 
@@ -115,6 +122,12 @@ SIGNATURES = {
                                                    C.c_int32, _i32p, _i32p]),
     "ll_balance_layouts": (C.c_int, [_i32p, _i32p, _f64p, _f64p, _u64p, C.c_int32, C.c_double, C.c_double, C.c_double,
                                      C.c_double]),
+    "ll_sim_reset": (C.c_int, [_ctx, C.c_int32, C.c_double, C.c_double, C.POINTER(SimView)]),
+    "ll_sim_update": (C.c_int, [_ctx, C.c_int32, C.POINTER(SimView)]),
+    "ll_sim_get": (C.c_int, [_ctx, C.POINTER(SimView)]),
+    "ll_sim_set": (C.c_int, [_ctx, C.POINTER(SimView), C.POINTER(SimView)]),
+    "ll_sim_step_penalty": (C.c_int, [_ctx, C.c_int32, _f64p]),
+    "ll_sim_terminal_penalty": (C.c_int, [_ctx, C.c_int32, C.c_int32, _f64p, _f64p]),
     "ll_profile": (C.c_int, [_ctx, C.c_int]),
     "ll_kernel_times_get": (C.c_int, [_ctx, C.POINTER(KernelTimes), C.c_int]),
     "ll_step_counter": (C.c_int, [_ctx, _f64p, _u64p, C.c_int]),

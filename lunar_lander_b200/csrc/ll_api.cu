@@ -10,7 +10,7 @@
 size_t ll_stats_partial_bytes(unsigned long long pop_local);
 int ll_file_write(ll_ctx* ctx, const char* path, const char* name, int digits, const std::vector<double>& elites_canon);
 int ll_file_read(const char* path, std::vector<uint64_t>* sizes, uint64_t* pop, uint64_t* top, uint64_t* epochs, int* act, int* strategy,
-                 double* ratio, std::string* name, std::vector<double>* elites_canon, std::string* err);
+                 double* ratio, std::string* name, std::vector<double>* elites_canon, std::string* err, uint64_t* generator_word0 = nullptr);
 
 namespace
 {
@@ -183,7 +183,7 @@ extern "C" void ll_destroy(ll_ctx* ctx)
         }
     void* ptrs[] = {ctx->d_params, ctx->d_elites,   ctx->d_dev2canon, ctx->d_layouts, ctx->d_fitness, ctx->d_lr,        ctx->d_steps,
                     ctx->d_ep_steps, ctx->d_ep_fit, ctx->d_queue,     ctx->d_stats,   ctx->d_partials, ctx->d_sel,      ctx->d_keys,
-                    ctx->d_cand,   ctx->d_elite_idx, ctx->d_trace,    ctx->d_scratch};
+                    ctx->d_cand,   ctx->d_elite_idx, ctx->d_trace,    ctx->d_scratch, ctx->d_sim};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (ctx->h_pin) cudaFreeHost(ctx->h_pin);
@@ -777,7 +777,8 @@ extern "C" int ll_deserialize(ll_ctx* ctx, const char* path)
     double r = 0.0;
     std::string nm, err;
     std::vector<double> canon;
-    const int rc = ll_file_read(path, &s, &p, &t, &e, &a, &st, &r, &nm, &canon, &err);
+    uint64_t gen0 = ~0ull;
+    const int rc = ll_file_read(path, &s, &p, &t, &e, &a, &st, &r, &nm, &canon, &err, &gen0);
     if (rc != LL_OK) return ll_fail(ctx, rc, err);
     if (s != ctx->sizes) return ll_fail(ctx, LL_EINVAL, "ll_deserialize: the file's vSize does not match this context's topology");
     if (t != ctx->top) return ll_fail(ctx, LL_EINVAL, "ll_deserialize: the file's nTop does not match this context");
@@ -796,6 +797,7 @@ extern "C" int ll_deserialize(ll_ctx* ctx, const char* path)
     LL_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     LL_CUDA(ctx, cudaMemcpy(ctx->d_elites, host.data(), host.size(), cudaMemcpyHostToDevice));
     ctx->has_elites = true, ctx->epochs = e, ctx->strategy = st, ctx->ratio = r;
+    if (gen0 != ~0ull) ctx->seed = gen0 & 0xffffffffull; // the generator line carries the GA key of the run that wrote the file
     // the file holds the parent set only; slots [top, pop) are rebuilt exactly as the CreatePopulation that
     // preceded the save built them (generation key = stored epoch count)
     scope sc(ctx, CLS_MUTATE, 1);

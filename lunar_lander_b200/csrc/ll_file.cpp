@@ -60,11 +60,23 @@ int ll_file_write(ll_ctx* ctx, const char* path, const char* name, int digits, c
             }
         }
     f << "vWeights_end\n";
-    // The GA here is Philox-keyed, so there is no sequential generator state to save; the line keeps the shape of
-    // the sample files (624 words, the stream form of a std::mt19937 in libc++) with a freshly seeded engine.
+    // The GA here is Philox-keyed, so there is no sequential generator state to save; the line keeps the shape of the
+    // sample files (624 words = the stream form of a std::mt19937 in libc++) with the state of a freshly seeded engine,
+    // whose first word is the seed itself: ll_file_read takes the Philox key back from it, so a resumed run continues
+    // with the generator of the run that wrote the file (as Deserialize restores the mt19937 in the reference).
     f << "generator";
-    std::mt19937 eng(static_cast<uint32_t>(ctx->seed));
-    for (int i = 0; i < 624; ++i) f << " " << eng();
+    {
+        std::mt19937 eng(static_cast<uint32_t>(ctx->seed));
+        std::ostringstream os;
+        os << eng;
+        std::istringstream is(os.str());
+        for (int i = 0; i < 624; ++i)
+        {
+            unsigned long w = 0;
+            is >> w;
+            f << " " << w;
+        }
+    }
     f << "\n";
     f.flush();
     if (!f) return ll_fail(ctx, LL_EIO, std::string("write failed: ") + path);
@@ -72,7 +84,7 @@ int ll_file_write(ll_ctx* ctx, const char* path, const char* name, int digits, c
 }
 
 int ll_file_read(const char* path, std::vector<uint64_t>* sizes, uint64_t* pop, uint64_t* top, uint64_t* epochs, int* act, int* strategy,
-                 double* ratio, std::string* name, std::vector<double>* elites_canon, std::string* err)
+                 double* ratio, std::string* name, std::vector<double>* elites_canon, std::string* err, uint64_t* generator_word0)
 {
     auto bad = [&](const std::string& m) {
         *err = std::string(path) + ": " + m;
@@ -149,6 +161,11 @@ int ll_file_read(const char* path, std::vector<uint64_t>* sizes, uint64_t* pop, 
     }
     for (char s : seen)
         if (!s) return bad("missing pop/layer block");
-    // "generator": 624 (libc++) or 625 (libstdc++) integers follow; the Philox GA does not consume them.
+    // "generator": 624 (libc++) or 625 (libstdc++) integers follow; only the first one is used (the Philox key)
+    if (generator_word0)
+    {
+        uint64_t w = 0;
+        if ((f >> tok) && tok == "generator" && (f >> w)) *generator_word0 = w;
+    }
     return LL_OK;
 }

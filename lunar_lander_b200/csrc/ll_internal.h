@@ -106,6 +106,9 @@ struct ll_ctx
     ll_step_rec* d_trace    = nullptr;
     int trace_cap = 0;
     void* d_scratch = nullptr; // small scratch (feedforward state, episode result)
+    void* d_sim     = nullptr; // ll_sim.cu: the single stepped lander (state, view, penalties), allocated on first use
+    bool sim_ready = false, sim_custom = false;
+    double sim_lpad_x1 = 0.0, sim_init_x = 0.0;
 
     // pinned host staging
     void* h_pin = nullptr;

@@ -189,3 +189,23 @@ def ref_make_layouts(config_path, base_seed, n, directions=None, extra=None):
 def ref_threads() -> int:
     lib = ref()
     return int(lib.ref_threads()) if lib is not None else 0
+
+
+def ref_nn_play(config_path, weight_file, seed=None, force_ltr=False, force_rtl=False, fps=60.0, max_frames=6000, extra=None):
+    """main.py --mode=nn_play headless, on the reference's own GameLogicCpp<double> (ref_harness.cpp: ref_nn_play)."""
+    lib = ref()
+    oi = (C.c_int * 6)()
+    of = (C.c_double * 4)()
+    rec = np.zeros((max_frames, 6))
+    ov = ";".join(f"{k}={v}" for k, v in (extra or {}).items())
+    lib.ref_nn_play.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int,
+                                C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_int]
+    lib.ref_last_error.restype = C.c_char_p
+    rc = lib.ref_nn_play(config_path.encode(), ov.encode(), weight_file.encode(), int(seed is not None), 0 if seed is None else seed,
+                         int(force_ltr), int(force_rtl), fps, max_frames, oi, of, rec.ctypes.data_as(C.POINTER(C.c_double)), max_frames)
+    if rc:
+        raise RuntimeError(lib.ref_last_error().decode())
+    n = oi[3]
+    return dict(spad_x1=oi[0], lpad_x1=oi[1], frames=oi[2], steps=n, start_frame=oi[4], landed=bool(oi[5] & 1), crashed=bool(oi[5] & 2),
+                landed_successfully=bool(oi[5] & 4), game_over=bool(oi[5] & 8), penalty=of[0], x=of[1], y=of[2], fuel=of[3],
+                actions=rec[:n, 0].astype(int), states=rec[:n, 1:].copy())

@@ -237,6 +237,69 @@ extern "C"
         }
     }
 
+    // main.py --mode=nn_play without the window (main.py:127-238): the reference's GameLogicCpp<double> and
+    // generate_random_pad_positions, the shim network loaded from `weight_file` (mod_nn_play.py:25-59), the UI loop's start
+    // gating with time = frame / fps, penalty accumulated in a Python float (double).  Test-only counterpart of
+    // lunar_lander_b200/nn_play.py.  rec (may be null): per update 6 doubles = action, state[0..4].
+    int ref_nn_play(const char* cfg, const char* ov, const char* weight_file, int has_seed, int seed, int force_ltr,
+                    int force_rtl, double fps, int max_frames, int* out_int /*spad,lpad,frames,steps,start_frame,flags*/,
+                    double* out_f64 /*penalty,x,y,fuel*/, double* rec, int cap)
+    {
+        try
+        {
+            apply_overrides(cfg, ov);
+            GameLogicCpp<double> logic(true);
+            auto pads = generate_random_pad_positions(Config::getDouble("DisplayCfg.width"),
+                                                      static_cast<int>(Config::getDouble("GameCfg.spad_width")),
+                                                      static_cast<int>(Config::getDouble("GameCfg.lpad_width")),
+                                                      has_seed ? std::optional<int>(seed) : std::nullopt, force_ltr != 0,
+                                                      force_rtl != 0);
+            logic.reset(static_cast<double>(pads.first), static_cast<double>(pads.second));
+            nn::ANN_MLP_GA<double> net;
+            net.Deserialize(weight_file);
+            double state[5] = {0, 0, 0, 0, 0};
+            bool started = false, over = false;
+            double penalty = 0.0;
+            int steps = 0, frame = 0, start_frame = -1;
+            while (frame < max_frames && !over)
+            {
+                int action = 0;
+                logic.get_state(state, 5);
+                const int nn_action = static_cast<int>(net.feedforward(state, 5, 0));
+                if (!started)
+                {
+                    const double elapsed_ms = frame * 1000.0 / fps;
+                    if (elapsed_ms > 2000) action = 1, started = true;
+                    else if (nn_action != 0) action = 1, started = true;
+                    if (started) start_frame = frame;
+                }
+                else action = nn_action;
+                if (started)
+                {
+                    const bool done = logic.update(action, state, 5);
+                    penalty += logic.calculate_step_penalty(action);
+                    if (rec && steps < cap)
+                    {
+                        rec[steps * 6] = action;
+                        for (int i = 0; i < 5; ++i) rec[steps * 6 + 1 + i] = state[i];
+                    }
+                    ++steps;
+                    if (done) over = true;
+                }
+                if (over) penalty += logic.calculate_terminal_penalty(steps);
+                ++frame;
+            }
+            out_int[0] = pads.first, out_int[1] = pads.second, out_int[2] = frame, out_int[3] = steps, out_int[4] = start_frame;
+            out_int[5] = (logic.landed ? 1 : 0) | (logic.crashed ? 2 : 0) | (logic.landed_successfully ? 4 : 0) | (over ? 8 : 0);
+            out_f64[0] = penalty, out_f64[1] = logic.x, out_f64[2] = logic.y, out_f64[3] = logic.fuel;
+            return 0;
+        } catch (const std::exception& e)
+        {
+            g_err = e.what();
+            return 1;
+        }
+    }
+
     // GA of the shim, exposed so the product's GA kernels can be checked against it.
     // params: [pop][P] canonical, in/out.  has_elites: 0 -> initial population, 1 -> children of slots [0,top).
     int ref_create_population_f64(const uint64_t* sizes, int n_sizes, int seed, uint64_t pop, uint64_t top, uint64_t epochs,

@@ -207,7 +207,13 @@ namespace nn
             fwd_.assign(pop_ * P_, T(0));
             read_section(f, "vBiases_start", "vBiases_end", true);
             read_section(f, "vWeights_start", "vWeights_end", false);
-            // "generator": 624 (libc++) or 625 (libstdc++) integers; the Philox GA does not use them.
+            // "generator": 624 (libc++) or 625 (libstdc++) integers; the first one keys the Philox GA (state word 0 of a
+            // freshly seeded mt19937 = its seed), the way the real Deserialize restores its mt19937 from this line.
+            {
+                std::string gtok;
+                unsigned long w0 = 0;
+                if ((f >> gtok) && gtok == "generator" && (f >> w0)) seed_ = static_cast<uint32_t>(w0);
+            }
             for (size_t r = 0; r < top_; ++r) rebuild_forward(r);
             has_elites_ = true;
             // The file holds only the elites; the rest of the population is rebuilt exactly as the

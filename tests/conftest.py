@@ -19,7 +19,8 @@ def built():
     import __graft_entry__ as g
     lib = os.path.join(ROOT, "lunar_lander_b200", "libll_gpu.so")
     port = os.path.join(ROOT, "oracle", "_build", "libll_oracle.so")
-    if not (os.path.exists(lib) and os.path.exists(port)):
+    host = os.path.join(ROOT, "lunar_lander_b200", "host", "bin", "main_train_d")
+    if not (os.path.exists(lib) and os.path.exists(port) and os.path.exists(host)):
         g.build()
     return True
 

@@ -1,0 +1,143 @@
+"""The C++ host mirror (lunar_lander_b200/host: Config, nn::ANN_MLP_GA<T>, Training::NNEngineTrainer<T>, main_train_d/_f)
+against the reference's own main_train compiled unchanged (oracle/_ref/main_train_d/_f, built from /root/reference/src by
+oracle/Makefile with the ma-libs stand-ins): same config.txt, same seeds ->
+  * identical console log (generation blocks, best member, fitness to 4 decimals, stagnation resets) except wall times,
+  * identical checkpoint files up to the `generator` line, identical file names,
+  * identical behaviour of --continue (resume from <name>_last.txt) and of the unreachable --step file name.
+Reference interfaces: src/main_train.cpp:14-106, src/nn_engine_trainer.cpp:67-438.
+"""
+import os
+import re
+import subprocess
+
+import pytest
+
+from util import CFG_PATH, ROOT
+
+BIN = os.path.join(ROOT, "lunar_lander_b200", "host", "bin")
+REF = os.path.join(ROOT, "oracle", "_ref")
+
+pytestmark = pytest.mark.gpu
+
+
+def write_config(dirname, **ov):
+    lines = []
+    with open(CFG_PATH) as f:
+        for line in f:
+            key = line.split("=", 1)[0].strip() if "=" in line else None
+            if key in ov:
+                line = f"{key} = {ov.pop(key)}\n"
+            lines.append(line)
+    for k, v in ov.items():
+        lines.append(f"{k} = {v}\n")
+    os.makedirs(dirname, exist_ok=True)
+    with open(os.path.join(dirname, "config.txt"), "w") as f:
+        f.writelines(lines)
+
+
+def run(binary, cwd, *args):
+    p = subprocess.run([binary, *args], cwd=cwd, capture_output=True, text=True, timeout=600)
+    return p.returncode, p.stdout, p.stderr
+
+
+def normalise(log):
+    """drop the only run-dependent part of the log: wall times"""
+    return re.sub(r"\(Took: \d+:\d+, Total: \d+:\d+\)", "(Took: T, Total: T)", log)
+
+
+def weight_file_body(path):
+    with open(path) as f:
+        text = f.read()
+    head, sep, _ = text.partition("generator")
+    assert sep, f"{path}: no generator line"
+    return head
+
+
+def both(tmp_path, suffix, args=(), gpu_args=(), **ov):
+    ours, ref = str(tmp_path / "ours"), str(tmp_path / "ref")
+    for d in (ours, ref):
+        if not os.path.exists(os.path.join(d, "config.txt")):
+            write_config(d, **ov)
+    ref_bin = os.path.join(REF, "main_train_" + suffix)
+    if not os.path.exists(ref_bin):
+        pytest.skip("oracle/_ref was not built (needs /root/reference at build time)")
+    r_ref = run(ref_bin, ref, *args)
+    r_our = run(os.path.join(BIN, "main_train_" + suffix), ours, *args, *gpu_args)
+    return ours, ref, r_our, r_ref
+
+
+def compare_runs(ours, ref, r_our, r_ref):
+    assert r_ref[0] == 0, r_ref[2]
+    assert r_our[0] == 0, r_our[2]
+    assert normalise(r_our[1]) == normalise(r_ref[1])
+    files_ref = sorted(os.listdir(os.path.join(ref, "data")))
+    files_our = sorted(os.listdir(os.path.join(ours, "data")))
+    assert files_our == files_ref and files_ref
+    for name in files_ref:
+        assert weight_file_body(os.path.join(ours, "data", name)) == weight_file_body(os.path.join(ref, "data", name)), name
+    return files_ref
+
+
+SMALL = {"NNConfig.epochs": 12, "NNConfig.population_size": 48, "NNTrainingCfg.layout_nb": 6, "NNConfig.save_interval": 5,
+         "NNTrainingCfg.reset_period": 2}
+
+
+def test_main_train_d_matches_reference_log_and_files(tmp_path, built):
+    ours, ref, r_our, r_ref = both(tmp_path, "d", **SMALL)
+    files = compare_runs(ours, ref, r_our, r_ref)
+    assert "lunar_lander_last.txt" in files and "lunar_lander_5_16_16_4_s_0010.txt" in files
+    assert "Stagnation detected" in r_ref[1], "the case is meant to cover a layout reset"
+    assert "ll_episode_kernel<double,exact>" in r_our[2]
+
+
+def test_continue_resumes_like_the_reference(tmp_path, built):
+    ours, ref, r_our, r_ref = both(tmp_path, "d", **SMALL)
+    compare_runs(ours, ref, r_our, r_ref)
+    ours, ref, r_our, r_ref = both(tmp_path, "d", args=("--continue",))
+    files = compare_runs(ours, ref, r_our, r_ref)
+    assert "Successfully loaded network from checkpoint 'last'." in r_our[1]
+    assert "--- Generation 13 ---" in r_our[1] and "lunar_lander_5_16_16_4_s_0024.txt" in files
+
+
+def test_deep_topology_and_device_select(tmp_path, built):
+    """BASELINE configs[4]'s topology through the trainer; GpuCfg.select = device (radix top-k) gives the log of the host
+    std::sort path whenever fitness values are distinct (they are here: the log's best member / fitness agree)."""
+    ov = dict(SMALL)
+    ov.update({"NNConfig.hlayers": "8,16,32,16,8", "NNConfig.epochs": 6, "NNConfig.population_size": 96})
+    ours, ref, r_our, r_ref = both(tmp_path, "d", gpu_args=("--set", "GpuCfg.select=device"), **ov)
+    compare_runs(ours, ref, r_our, r_ref)
+
+
+def test_main_train_f_exact_mode_matches_reference(tmp_path, built):
+    ours, ref, r_our, r_ref = both(tmp_path, "f", gpu_args=("--set", "GpuCfg.mode=exact"), **SMALL)
+    compare_runs(ours, ref, r_our, r_ref)
+    assert "Using data type: float" in r_our[1]
+
+
+def test_main_train_f_fast_mode_trains(tmp_path, built):
+    """default float build = throughput mode (tensor-core kernel): not bit-comparable, must run and improve or hold the best"""
+    d = str(tmp_path / "fast")
+    ov = dict(SMALL)
+    ov.update({"NNConfig.hlayers": "16,64,32", "NNConfig.population_size": 512, "NNConfig.epochs": 8})
+    write_config(d, **ov)
+    rc, out, err = run(os.path.join(BIN, "main_train_f"), d)
+    assert rc == 0, err
+    best = [float(x) for x in re.findall(r"Best Avg Fitness: (-?[\d.]+)", out)]
+    assert len(best) == 8
+    assert "ll_episode_mma_kernel" in err
+    assert os.path.exists(os.path.join(d, "data", "lunar_lander_last.txt"))
+
+
+def test_step_checkpoint_name_quirk_and_bad_arguments(tmp_path, built):
+    """--step N looks for <name>_gen_000N.txt, a name save() never writes (src/main_train.cpp:48 vs nn_engine_trainer.cpp:161)"""
+    d = str(tmp_path / "q")
+    write_config(d, **dict(SMALL, **{"NNConfig.epochs": 1}))
+    rc, out, err = run(os.path.join(BIN, "main_train_d"), d, "--step", "3")
+    assert "Attempting to load network from checkpoint: gen_0003" in out
+    assert "File not found" in err and "lunar_lander_gen_0003.txt" in err
+    rc, out, err = run(os.path.join(BIN, "main_train_d"), d, "--step", "abc")
+    assert rc == 1 and "not a valid integer" in err
+    rc, out, err = run(os.path.join(BIN, "main_train_d"), d, "--step")
+    assert rc == 1 and "requires an integer argument" in err
+    rc, out, err = run(os.path.join(BIN, "main_train_d"), str(tmp_path))  # no config.txt there
+    assert rc == 1 and "FATAL: Could not load configuration" in err

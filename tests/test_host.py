@@ -49,6 +49,25 @@ def test_no_cpu_fallback(ll):
     assert _abi.lib.ll_microbench_fma(0, 32, 0.01, C.byref(v), None) == 2
 
 
+def test_cpp_host_trainer_refuses_without_gpu(built, tmp_path):
+    """main_train_d (the C++ mirror of src/main_train.cpp) reads config.txt like the reference and, with no CUDA device,
+    exits 1 with the library's message instead of training on the CPU."""
+    import shutil
+    import torch
+    exe = os.path.join(util.ROOT, "lunar_lander_b200", "host", "bin", "main_train_d")
+    assert os.path.exists(exe)
+    rc = subprocess.run([exe], cwd=tmp_path, capture_output=True, text=True)
+    assert rc.returncode == 1 and "FATAL: Could not load configuration from config.txt" in rc.stderr
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    shutil.copy(util.CFG_PATH, tmp_path / "config.txt")
+    rc = subprocess.run([exe], cwd=tmp_path, capture_output=True, text=True)
+    assert rc.returncode == 1 and "Using data type: double" in rc.stdout
+    assert "no CUDA device" in rc.stderr and "Failed to initialize NNEngineTrainer." in rc.stderr
+    out = subprocess.run(["ldd", exe], capture_output=True, text=True).stdout
+    assert "libll_gpu.so" in out and "oracle" not in out
+
+
 def test_product_does_not_link_the_oracle(ll):
     from lunar_lander_b200 import _abi
     out = subprocess.run(["ldd", _abi.LIB_PATH], capture_output=True, text=True).stdout
