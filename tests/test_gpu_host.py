@@ -99,13 +99,28 @@ def test_continue_resumes_like_the_reference(tmp_path, built):
     assert "--- Generation 13 ---" in r_our[1] and "lunar_lander_5_16_16_4_s_0024.txt" in files
 
 
-def test_deep_topology_and_device_select(tmp_path, built):
-    """BASELINE configs[4]'s topology through the trainer; GpuCfg.select = device (radix top-k) gives the log of the host
-    std::sort path whenever fitness values are distinct (they are here: the log's best member / fitness agree)."""
+def test_deep_topology_host_select(tmp_path, built):
+    """BASELINE configs[4]'s topology (8_16_32_16_8) through the trainer, host std::sort selection: identical to the reference"""
+    ov = dict(SMALL)
+    ov.update({"NNConfig.hlayers": "8,16,32,16,8", "NNConfig.epochs": 6, "NNConfig.population_size": 96})
+    ours, ref, r_our, r_ref = both(tmp_path, "d", gpu_args=("--set", "GpuCfg.select=host"), **ov)
+    compare_runs(ours, ref, r_our, r_ref)
+
+
+def test_device_select_differs_only_in_tie_order(tmp_path, built):
+    """GpuCfg.select = device ranks by (fitness, index); the reference's unstable std::sort may order members of EQUAL fitness
+    differently (random nets that repeat one action fly identical trajectories), which can swap a low-ranked parent.  The
+    best member, its fitness and the landing count per generation are the reference's; the population mean stays close."""
     ov = dict(SMALL)
     ov.update({"NNConfig.hlayers": "8,16,32,16,8", "NNConfig.epochs": 6, "NNConfig.population_size": 96})
     ours, ref, r_our, r_ref = both(tmp_path, "d", gpu_args=("--set", "GpuCfg.select=device"), **ov)
-    compare_runs(ours, ref, r_our, r_ref)
+    assert r_our[0] == 0 and r_ref[0] == 0, r_our[2]
+    pick = lambda log, pat: re.findall(pat, log)
+    for pat in (r"Best Avg Fitness: (\S+) \(Member (\d+)\)", r"Both Directions: (\d+)", r"--- (Generation \d+|Stagnation[^-]*) ---"):
+        assert pick(r_our[1], pat) == pick(r_ref[1], pat) and pick(r_ref[1], pat)
+    mean_our = [float(x) for x in pick(r_our[1], r"Avg Fitness:\s+(\S+)")]
+    mean_ref = [float(x) for x in pick(r_ref[1], r"Avg Fitness:\s+(\S+)")]
+    assert len(mean_our) == 6 and all(abs(a - b) <= 0.05 * abs(b) for a, b in zip(mean_our, mean_ref))
 
 
 def test_main_train_f_exact_mode_matches_reference(tmp_path, built):

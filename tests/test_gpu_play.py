@@ -76,13 +76,14 @@ def test_known_answers_constant_actions(mods):
     g = util.golden()
     logic = llc.GameLogicCppDouble(True, CFG_PATH)
     buf = np.zeros(5)
-    logic.reset()
+    ka = g["env_known_answers"][0]
+    logic.reset(ka["spad_x1"], ka["lpad_x1"])
     n = 0
     while not logic.update(0, buf):
         n += 1
     assert n + 1 == 9 and logic.crashed and logic.landed and not logic.landed_successfully
     assert logic.calculate_terminal_penalty(9) == pytest.approx(117.125, abs=1e-12)
-    logic.reset()
+    logic.reset(ka["spad_x1"], ka["lpad_x1"])
     for _ in range(5000):
         done = logic.update(1, buf)
     assert not done and logic.fuel == 0.0
