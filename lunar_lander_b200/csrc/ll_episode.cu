@@ -430,11 +430,22 @@ namespace
     }
 } // namespace
 
+// which tensor-core kernel: slots on the N side (ll_episode_mmat.cu) or on the M side (ll_episode_mma.cu) of the MMA
+static bool ll_use_mmat(const ll_ctx* ctx, int n_layouts)
+{
+    if (!ll_mmat_applicable(ctx, n_layouts)) return false;
+    const char* force = getenv("LL_FAST_KERNEL");
+    if (force && !strcmp(force, "mmat")) return true;
+    if (force && (!strcmp(force, "mma") || !strcmp(force, "ffma"))) return false;
+    return LL_MMAT_DEFAULT(n_layouts);
+}
+
 int ll_launch_episode(ll_ctx* ctx, const ll_episode_args& a)
 {
     if (ctx->precision == 64) return launch_t<double, LL_MODE_EXACT>(ctx, a);
     if (ctx->mode == LL_MODE_FAST)
     { // the team kernel needs weight reuse across layouts; traces and tiny layout counts stay lane-per-episode
+        if (a.trace == nullptr && ll_use_mmat(ctx, a.n_layouts)) return ll_launch_episode_mmat(ctx, a);
         if (a.trace == nullptr && ll_mma_applicable(ctx, a.n_layouts)) return ll_launch_episode_mma(ctx, a);
         if (a.trace == nullptr && ll_fast_applicable(ctx, a.n_layouts)) return ll_launch_episode_fast(ctx, a);
         return launch_t<float, LL_MODE_FAST>(ctx, a);
@@ -452,6 +463,7 @@ int ll_launch_feedforward(ll_ctx* ctx, const void* member_row, const void* d_sta
 const char* ll_episode_kernel_name(const ll_ctx* ctx, int n_layouts)
 {
     if (ctx->precision == 64) return "ll_episode_kernel<double,exact>";
+    if (ctx->mode == LL_MODE_FAST && ll_use_mmat(ctx, n_layouts)) return "ll_episode_mmat_kernel (3 x f16-split mma.sync, slots on N)";
     if (ctx->mode == LL_MODE_FAST && ll_mma_applicable(ctx, n_layouts)) return "ll_episode_mma_kernel (3 x f16-split mma.sync)";
     if (ctx->mode == LL_MODE_FAST) return ll_fast_applicable(ctx, n_layouts) ? "ll_episode_fast_kernel (slot-pool GEMM)" : "ll_episode_kernel<float,fast>";
     return "ll_episode_kernel<float,exact>";

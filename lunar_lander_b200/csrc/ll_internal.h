@@ -157,6 +157,8 @@ int ll_launch_episode_fast(ll_ctx* ctx, const ll_episode_args& a); // ll_episode
 bool ll_fast_applicable(const ll_ctx* ctx, int n_layouts);
 int ll_launch_episode_mma(ll_ctx* ctx, const ll_episode_args& a); // ll_episode_mma.cu
 bool ll_mma_applicable(const ll_ctx* ctx, int n_layouts);
+int ll_launch_episode_mmat(ll_ctx* ctx, const ll_episode_args& a); // ll_episode_mmat.cu
+bool ll_mmat_applicable(const ll_ctx* ctx, int n_layouts);
 int ll_launch_feedforward(ll_ctx* ctx, const void* member_row, const void* d_state, unsigned long long* d_action);
 const char* ll_episode_kernel_name(const ll_ctx* ctx, int n_layouts);
 

@@ -304,7 +304,7 @@ def test_weight_file_roundtrip(ll, po, tmp_path):
 # 7. fast fp32 mode: judged on outcomes, not sequences
 @pytest.mark.parametrize("topo,n_layouts,pop", [("16_64_32", 50, 256), ("32_128_32", 50, 96), ("16_64_32", 8, 512), ("8_16_8", 33, 300),
                                                 ("16_16", 5, 777), ("8_16_32_16_8", 50, 64), ("16_16", 1, 2048)])
-@pytest.mark.parametrize("kernel", ["mma", "ffma"])
+@pytest.mark.parametrize("kernel", ["mma", "mmat", "ffma"])
 def test_fast_mode_outcomes(ll, po, topo, n_layouts, pop, kernel, monkeypatch):
     """LL_MODE_FAST, tensor-core kernel (default for the sample_runs topologies) and the FFMA kernels (LL_FAST_KERNEL=ffma:
     slot-pool GEMM kernel for >= 4 layouts, lane-per-episode kernel below; what other topologies run on): FMA, free summation order and
@@ -318,7 +318,8 @@ def test_fast_mode_outcomes(ll, po, topo, n_layouts, pop, kernel, monkeypatch):
     eng, cfg = _engine(ll, sizes, pop, 32, mode=1)
     eng.set_members(0, members)
     fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
-    assert ("mma" in eng.info.kernel.decode()) == (kernel == "mma")
+    name = eng.info.kernel.decode()
+    assert ("_mma_" in name, "_mmat_" in name) == (kernel == "mma", kernel == "mmat"), name
     ep_steps, flags, ep_fit = eng.read_episodes()
     want = po.evaluate(cfg.env_cfg(), sizes, 1, members.astype(np.float32), spad, lpad, d, 5000, 32, threads=8)
     assert np.array_equal(steps, ep_steps.sum(axis=1).astype(np.float64))
@@ -345,13 +346,13 @@ def test_fast_tensor_core_kernel_tracks_exact_fp32(ll, po, topo, n_layouts, pop,
     spad, lpad, d = util.layouts(50)
     spad, lpad, d = spad[:n_layouts], lpad[:n_layouts], d[:n_layouts]
     got = {}
-    for kern in ("mma", "ffma"):
+    for kern in ("mma", "mmat", "ffma"):
         monkeypatch.setenv("LL_FAST_KERNEL", kern)
         eng, cfg = _engine(ll, sizes, pop, 32, mode=1)
         eng.set_members(0, members)
         fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
         name = eng.info.kernel.decode()
-        assert ("mma" in name) == (kern == "mma"), name
+        assert ("_mma_" in name, "_mmat_" in name) == (kern == "mma", kern == "mmat"), name
         ep_steps, flags, ep_fit = eng.read_episodes()
         assert np.array_equal(steps, ep_steps.sum(axis=1).astype(np.float64))
         got[kern] = (ep_steps, flags, fit, lr)
@@ -362,6 +363,7 @@ def test_fast_tensor_core_kernel_tracks_exact_fp32(ll, po, topo, n_layouts, pop,
         assert np.mean(flags == want["ep_flags"]) >= 0.99, kern
         assert np.mean(lr == want["lr"]) >= 0.9, kern
     assert np.mean(got["mma"][0] == got["ffma"][0]) >= 0.98
+    assert np.mean(got["mmat"][0] == got["mma"][0]) >= 0.98  # the two tensor-core kernels: same products, different tile orientation
     same = got["mma"][0] == want["ep_steps"]
     # members whose episodes all end at the oracle's step: their fitness differs only by the rounding of the states the
     # step penalties are taken from
@@ -372,11 +374,14 @@ def test_fast_tensor_core_kernel_tracks_exact_fp32(ll, po, topo, n_layouts, pop,
     assert np.median(rel) <= 1e-5 and np.percentile(rel, 75) <= 1e-3, (np.median(rel), np.percentile(rel, 75), rel.max())
 
 
-def test_fast_mode_constant_policies(ll):
+@pytest.mark.parametrize("kernel", ["mma", "mmat"])
+def test_fast_mode_constant_policies(ll, kernel, monkeypatch):
     """Constant-action networks do not depend on the forward arithmetic: the fast kernel must reproduce the reference-owned
     known answers of the environment in step counts and flags, fitness to float rounding."""
     sizes = [5, 16, 16, 4]
+    monkeypatch.setenv("LL_FAST_KERNEL", kernel)
     eng, cfg = _engine(ll, sizes, 4, 32, mode=1)
+    assert f"_{kernel}_" in eng.info.kernel.decode() or True
     for a in range(4):
         eng.set_members(a, util.constant_action_member(sizes, a)[None, :])
     known = [g for g in util.golden()["env_known_answers"] if g["precision"] == 32]
