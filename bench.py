@@ -221,7 +221,11 @@ def ncu_traffic(workload, members):
 
 # HMMA work the tensor-core episode kernel really issues per lander step (ll_episode_mma.cu): per layer
 # ceil(in/16) * ceil(out/8) tiles x 3 split products x 16*8*16 MACs, for a 16-slot tile
-def hmma_flop_per_step(sizes):
+# (ll_episode_mmat.cu, slots on the N side: ceil(in/16) * ceil(out/16) tiles for an 8-slot tile)
+def hmma_flop_per_step(sizes, transposed=False):
+    if transposed:
+        tiles = sum(((sizes[i] + 15) // 16) * ((sizes[i + 1] + 15) // 16) for i in range(len(sizes) - 1))
+        return tiles * 3 * 2 * 16 * 8 * 16 / 8.0
     tiles = sum(((sizes[i] + 15) // 16) * ((sizes[i + 1] + 7) // 8) for i in range(len(sizes) - 1))
     return tiles * 3 * 2 * 16 * 8 * 16 / 16.0
 
@@ -413,8 +417,8 @@ def run_gpu(args):
             "tensor_pipe": ({"note": "explains the FMA-roofline fraction: HMMA flop the kernel issues (3 f16-split products, padded "
                                      "tiles, every row of the 16-slot tile whether its episode is live or not counted as live) "
                                      "against the measured mma.sync.m16n8k16.f16 rate",
-                             "hmma_flop_per_lander_step": hmma_flop_per_step(sizes),
-                             "achieved_live_rows": steps_local * hmma_flop_per_step(sizes) / (episode_ms_max * 1e-3) / 1e12 if episode_ms_max > 0 else None,
+                             "hmma_flop_per_lander_step": hmma_flop_per_step(sizes, "mmat" in eng.info.kernel.decode()),
+                             "achieved_live_rows": steps_local * hmma_flop_per_step(sizes, "mmat" in eng.info.kernel.decode()) / (episode_ms_max * 1e-3) / 1e12 if episode_ms_max > 0 else None,
                              "peak": hmma_peak.value, "unit": "TFLOP/s"} if "mma" in eng.info.kernel.decode() else None),
             "roofline_ga": {"bound": "hbm", "achieved": ga_gbs, "peak": hbm_peak, "unit": "GB/s",
                             "frac": ga_gbs / hbm_peak if hbm_peak else None, "traffic": None, "kernel": "ll_create_population_kernel",

@@ -20,7 +20,18 @@
 // exactly like the reference's accumulators (src/nn_engine_trainer.cpp:477-530).
 #include <stdio.h>
 
+#include <stdlib.h>
+#include <string.h>
+
 #include "ll_ops.cuh"
+
+// default choice between the two tensor-core kernels (measured on B200): up to 8 layouts fill one 8-slot
+// N tile of the transposed kernel exactly (configs[2]: 5.09e9 vs 3.48e9 lander-steps/s; configs[1]: 6.4e8 vs 6.0e8); with 50
+// layouts the 16-row M-side kernel keeps the edge (configs[3]: 85.8 % of the FMA roofline vs 76.8 % / 69.0 % for one / two
+// N tiles per warp)
+#ifndef LL_MMAT_DEFAULT
+#define LL_MMAT_DEFAULT(n_layouts) ((n_layouts) <= 8)
+#endif
 
 namespace
 {

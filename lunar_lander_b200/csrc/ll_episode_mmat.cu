@@ -8,7 +8,7 @@
 // and a 50-layout member drains its last episodes in tiles that are mostly empty.  Here the product is transposed:
 //     D[out x slots] = W[out x in] * X[in x slots],   M = 16 output neurons, N = 8 slots, K = 16 inputs per HMMA
 //   * an N tile is 8 slots: 8 layouts fill it completely, and a warp that owns 16 slots (two N tiles) skips the HMMAs, the
-//     epilogue and the environment of a tile whose 8 episodes have all ended (a warp-uniform branch);
+//     epilogue and the environment of a tile whose 8 episodes have all ended (a warp-uniform switch to a one-tile pass);
 //   * the weights are the A operand: split once per member into fp16 hi / scaled lo and stored as ready-made A fragments,
 //     one LDS.128 each per (output tile, k tile, lane), shared by the warp's N tiles; the bias is a float2 per (tile, g);
 //   * activations stay in registers: the D fragment of layer l (rows = outputs g / g+8, columns = slots 2t, 2t+1), after
@@ -96,7 +96,7 @@ namespace
     // layer's B fragments yh/yl[j][mt][2] (tanh applied, split, transposed), or for the output layer z[j][2] = tanh'd outputs
     // (row g, slots 2t and 2t+1).  Output tiles go in panels of PM so that the 3 * PM * NT accumulator tiles stay in registers.
     template <class N, int L, int NT>
-    __device__ __forceinline__ void layer_t(const float* __restrict__ sw, int lane, int g, unsigned mask, const uint32_t (&xh)[NT][N::k16(L) / 16][2],
+    __device__ __forceinline__ void layer_t(const float* __restrict__ sw, int lane, int g, const uint32_t (&xh)[NT][N::k16(L) / 16][2],
                                             const uint32_t (&xl)[NT][N::k16(L) / 16][2], uint32_t (&yh)[NT][N::m16(L) / 16][2],
                                             uint32_t (&yl)[NT][N::m16(L) / 16][2], float (&z)[NT][2])
     {
@@ -132,18 +132,16 @@ namespace
                     const uint4 wl = W[(((mp + i) * KT + kt) * 2 + 1) * 32];
 #pragma unroll
                     for (int j = 0; j < NT; ++j)
-                        if (NT == 1 || (mask >> j) & 1u)
-                        {
-                            mma_w(acc[0][i][j], wh, xl[j][kt][0], xl[j][kt][1]);
-                            mma_w(acc[1][i][j], wl, xh[j][kt][0], xh[j][kt][1]);
-                            mma_w(acc[2][i][j], wh, xh[j][kt][0], xh[j][kt][1]);
-                        }
+                    {
+                        mma_w(acc[0][i][j], wh, xl[j][kt][0], xl[j][kt][1]);
+                        mma_w(acc[1][i][j], wl, xh[j][kt][0], xh[j][kt][1]);
+                        mma_w(acc[2][i][j], wh, xh[j][kt][0], xh[j][kt][1]);
+                    }
                 }
 #pragma unroll
             for (int i = 0; i < PM; ++i)
 #pragma unroll
                 for (int j = 0; j < NT; ++j)
-                    if (NT == 1 || (mask >> j) & 1u)
                     {
                         float v[4];
 #pragma unroll
@@ -166,13 +164,13 @@ namespace
 
     template <class N, int L, int NT> struct tchain
     {
-        static __device__ __forceinline__ void run(const float* __restrict__ sw, int lane, int g, unsigned mask,
+        static __device__ __forceinline__ void run(const float* __restrict__ sw, int lane, int g,
                                                    const uint32_t (&xh)[NT][N::k16(L) / 16][2], const uint32_t (&xl)[NT][N::k16(L) / 16][2],
                                                    float (&z)[NT][2])
         {
             uint32_t yh[NT][N::m16(L) / 16][2], yl[NT][N::m16(L) / 16][2];
-            layer_t<N, L, NT>(sw, lane, g, mask, xh, xl, yh, yl, z);
-            if constexpr (L + 1 < N::NL) tchain<N, L + 1, NT>::run(sw, lane, g, mask, yh, yl, z);
+            layer_t<N, L, NT>(sw, lane, g, xh, xl, yh, yl, z);
+            if constexpr (L + 1 < N::NL) tchain<N, L + 1, NT>::run(sw, lane, g, yh, yl, z);
         }
     };
 
@@ -299,7 +297,18 @@ namespace
                 float z[NT][2];
 #pragma unroll
                 for (int j = 0; j < NT; ++j) z[j][0] = 0.f, z[j][1] = 0.f;
-                tchain<N, 0, NT>::run(sw, lane, g, mask, xh, xl, z);
+                if (NT == 1 || mask == (1u << NT) - 1u) tchain<N, 0, NT>::run(sw, lane, g, xh, xl, z);
+                else
+                { // NT == 2 and the 8 episodes of one tile have all ended: a single-tile pass over the live one (warp-uniform)
+                    const bool first = (mask & 1u) != 0u;
+                    uint32_t sh[1][1][2], sl[1][1][2];
+                    float z1[1][2] = {{0.f, 0.f}};
+#pragma unroll
+                    for (int w = 0; w < 2; ++w) sh[0][0][w] = first ? xh[0][0][w] : xh[NT - 1][0][w], sl[0][0][w] = first ? xl[0][0][w] : xl[NT - 1][0][w];
+                    tchain<N, 0, 1>::run(sw, lane, g, sh, sl, z1);
+                    if (first) z[0][0] = z1[0][0], z[0][1] = z1[0][1];
+                    else z[NT - 1][0] = z1[0][0], z[NT - 1][1] = z1[0][1];
+                }
 
                 unsigned fin[NT];
                 bool done[NT], landed[NT], success[NT];

@@ -139,7 +139,7 @@ def test_main_train_f_fast_mode_trains(tmp_path, built):
     assert rc == 0, err
     best = [float(x) for x in re.findall(r"Best Avg Fitness: (-?[\d.]+)", out)]
     assert len(best) == 8
-    assert "ll_episode_mma_kernel" in err
+    assert "ll_episode_mmat_kernel" in err  # 6 layouts: the slots-on-N tensor-core kernel
     assert os.path.exists(os.path.join(d, "data", "lunar_lander_last.txt"))
 
 
