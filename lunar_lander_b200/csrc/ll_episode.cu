@@ -20,6 +20,7 @@
 // exactly like the reference's accumulators (src/nn_engine_trainer.cpp:477-530).
 #include <stdio.h>
 
+#include <algorithm>
 #include <stdlib.h>
 #include <string.h>
 
@@ -49,7 +50,8 @@ namespace
         int trace_cap;
         ll_episode_result* trace_result;
         // geometry
-        int G, nslots;            // lanes per member, members per warp tile
+        int G, nslots;            // episode slots per member, members per warp tile
+        int Q;                    // lanes per episode slot (the slot's output neurons are dealt to its Q lanes); G * nslots * Q <= 32
         unsigned int n_tiles;
         int slot_stride;          // elements between member rows in shared memory
         int off_w, off_act, off_fit, off_meta, warp_bytes; // byte offsets inside a warp's shared-memory slice
@@ -108,8 +110,11 @@ namespace
     }
 
     // Whole forward pass; returns the index of the first maximum of the output layer.
+    // Q > 1: the episode's column is shared by Q lanes (sub = 0..Q-1), each taking every Q-th tile of 4 output neurons; a neuron's
+    // own arithmetic (sequential-k multiply-add, bias last, activation) is untouched, so the result is bit-identical to Q == 1.
+    // Every lane of the warp must call this together when Q > 1 (warp barriers between layers).
     template <typename T, int MODE>
-    __device__ __forceinline__ int forward(const ll_topo& tp, const T* __restrict__ wrow, T* a0, T* a1)
+    __device__ __forceinline__ int forward(const ll_topo& tp, const T* __restrict__ wrow, T* a0, T* a1, int sub = 0, int Q = 1)
     {
         constexpr int BIG = sizeof(T) == 4 ? 16 : 8;
         T* ain  = a0;
@@ -119,17 +124,25 @@ namespace
             const int in = tp.in[l], op = tp.out_pad[l];
             const T* w = wrow + tp.w_off[l];
             const T* b = wrow + tp.b_off[l];
-            int o      = 0;
-            for (; o + BIG <= op; o += BIG) layer_tile<T, MODE, BIG>(w + o, b + o, ain, aout + o * 32, in, op, tp.activation);
-            if (BIG == 16 && o + 8 <= op)
+            if (Q > 1)
             {
-                layer_tile<T, MODE, 8>(w + o, b + o, ain, aout + o * 32, in, op, tp.activation);
-                o += 8;
+                for (int o = sub * 4; o < op; o += Q * 4) layer_tile<T, MODE, 4>(w + o, b + o, ain, aout + o * 32, in, op, tp.activation);
+                __syncwarp();
             }
-            if (o + 4 <= op)
+            else
             {
-                layer_tile<T, MODE, 4>(w + o, b + o, ain, aout + o * 32, in, op, tp.activation);
-                o += 4;
+                int o = 0;
+                for (; o + BIG <= op; o += BIG) layer_tile<T, MODE, BIG>(w + o, b + o, ain, aout + o * 32, in, op, tp.activation);
+                if (BIG == 16 && o + 8 <= op)
+                {
+                    layer_tile<T, MODE, 8>(w + o, b + o, ain, aout + o * 32, in, op, tp.activation);
+                    o += 8;
+                }
+                if (o + 4 <= op)
+                {
+                    layer_tile<T, MODE, 4>(w + o, b + o, ain, aout + o * 32, in, op, tp.activation);
+                    o += 4;
+                }
             }
             T* t = ain;
             ain  = aout;
@@ -143,6 +156,7 @@ namespace
             const T v = ain[j * 32];
             if (v > vbest) vbest = v, best = j;
         }
+        if (Q > 1) __syncwarp(); // the outputs are read before any lane overwrites the buffers with the next step's state
         return best;
     }
 
@@ -185,13 +199,15 @@ namespace
         uint64_t* bar     = reinterpret_cast<uint64_t*>(ws);
         int* next_layout  = reinterpret_cast<int*>(ws + 16);
         T* wsm            = reinterpret_cast<T*>(ws + a.off_w);
-        T* act0           = reinterpret_cast<T*>(ws + a.off_act) + lane;
+        const int Q = a.Q, sub = lane % Q, elane = lane / Q; // Q lanes share one episode slot (and its activation column)
+        T* act0           = reinterpret_cast<T*>(ws + a.off_act) + (lane - sub);
         T* act1           = act0 + tp.max_width * 32;
         double* res_fit   = reinterpret_cast<double*>(ws + a.off_fit);
         int* res_meta     = reinterpret_cast<int*>(ws + a.off_meta);
 
         const int G = a.G, L = a.n_layouts;
-        const int slot = lane / G, j = lane - slot * G;
+        const int slot = elane / G, j = elane - slot * G;
+        const unsigned gmask = (Q >= 32 ? 0xffffffffu : ((1u << Q) - 1u)) << (lane - sub);
         const T* wrow  = wsm + (size_t)min(slot, a.nslots - 1) * a.slot_stride; // surplus lane groups (slot >= nslots) idle
         const ll_layout<T>* layouts = static_cast<const ll_layout<T>*>(a.layouts);
         const uint32_t row_bytes    = (uint32_t)tp.p_dev * sizeof(T);
@@ -216,7 +232,7 @@ namespace
             __syncwarp();
             if (lane < nvalid)
                 ll_bulk_g2s(wsm + (size_t)lane * a.slot_stride, static_cast<const T*>(a.params) + (m0 + lane) * (size_t)tp.p_dev, row_bytes, bar);
-            if (j == 0) next_layout[slot] = min(G, L);
+            if (j == 0 && sub == 0) next_layout[slot] = min(G, L);
             __syncwarp();
             ll_mbar_wait(bar, phase);
             phase ^= 1u;
@@ -242,7 +258,7 @@ namespace
             while (__any_sync(0xffffffffu, active))
             {
                 write_state<T, MODE>(env, x, y, vx, vy, fuel, cx, act0);
-                const int action = forward<T, MODE>(tp, wrow, act0, act1);
+                const int action = forward<T, MODE>(tp, wrow, act0, act1, sub, Q);
                 if (active)
                 {
                     // apply_action: src/game_logic.cpp:156-183
@@ -306,9 +322,8 @@ namespace
                         const double fit = __dadd_rn((double)term, acc);
                         const int meta   = steps | (landed ? (1 << 28) : 0) | (crashed ? (1 << 29) : 0) | (success ? (1 << 30) : 0);
                         const int ridx   = slot * L + layout;
-                        res_fit[ridx]    = fit;
-                        res_meta[ridx]   = meta;
-                        if (a.ep_steps)
+                        if (sub == 0) res_fit[ridx] = fit, res_meta[ridx] = meta;
+                        if (a.ep_steps && sub == 0)
                         {
                             a.ep_steps[member * (size_t)L + layout] = meta;
                             a.ep_fit[member * (size_t)L + layout]   = fit;
@@ -322,7 +337,9 @@ namespace
                             if (success) r.bonus_lr[dir] = (double)O::add(T(0), env.tp_landed_lr_bonus);
                             *a.trace_result = r;
                         }
-                        const int nl = atomicAdd(&next_layout[slot], 1);
+                        int nl = 0; // the slot's Q lanes hold identical state and arrive here together
+                        if (sub == 0) nl = atomicAdd(&next_layout[slot], 1);
+                        if (Q > 1) nl = __shfl_sync(gmask, nl, lane - sub);
                         if (nl < L) begin_episode(nl);
                         else active = false;
                     }
@@ -332,7 +349,7 @@ namespace
 
             // ---- per-member totals in layout order: src/nn_engine_trainer.cpp:518-530
             __syncwarp();
-            if (valid && j == 0)
+            if (valid && j == 0 && sub == 0)
             {
                 double total = 0.0, total_steps = 0.0;
                 T bonus0 = T(0), bonus1 = T(0);
@@ -381,16 +398,34 @@ namespace
         a.ep_steps = h.ep_steps, a.ep_fit = h.ep_fit, a.queue = h.queue;
         a.trace = h.trace, a.trace_cap = h.trace_cap, a.trace_result = h.trace_result;
         const int L = h.n_layouts;
-        int G       = 32;
-        if (L < 32)
+        // Geometry of a warp tile: Q lanes per episode slot, G slots per member, nslots members.  Q = 1 (a lane walks all neurons of
+        // its episode) is the default.  LL_EXACT_Q = 2 | 4 | 8 deals a slot's output neurons to Q lanes; it is bit-identical (tested)
+        // but, measured on B200, SLOWER for the small populations it was meant for (configs[0], 100 x 50: 148 / 168 / 197 / 372 ms per
+        // generation for Q = 1 / 2 / 4 / 8): a generation lasts as long as its longest lane's chain of dependent fp64 operations, and
+        // with fewer slots per warp a member's layouts need more sequential rounds.  Kept as an experiment switch only.
+        auto geometry = [&](int q, int* g_out, int* nslots_out) {
+            const int E = 32 / q;
+            int G       = 1;
+            while (G < L && G < E) G <<= 1;
+            int nslots = E / G;
+            // a warp never stages more than ~48 KB of member rows: with few layouts and wide networks the tile holds
+            // fewer members than the warp has lane groups, and the surplus lanes idle
+            while (nslots > 1 && (size_t)nslots * tp.p_dev * sizeof(T) > (size_t)48 << 10) nslots >>= 1;
+            *g_out = G, *nslots_out = nslots;
+            return (unsigned long long)((h.n_members + nslots - 1) / nslots);
+        };
+        int Q = 1;
+        if (h.trace == nullptr)
         {
-            G = 1;
-            while (G < L) G <<= 1;
+            const char* force = getenv("LL_EXACT_Q");
+            if (force && *force)
+            {
+                const int f = atoi(force);
+                if (f == 1 || f == 2 || f == 4 || f == 8) Q = f;
+            }
         }
-        a.G = G, a.nslots = 32 / G;
-        // a warp never stages more than ~48 KB of member rows: with few layouts and wide networks the tile holds
-        // fewer members than the warp has lane groups, and the surplus lanes idle
-        while (a.nslots > 1 && (size_t)a.nslots * tp.p_dev * sizeof(T) > (size_t)48 << 10) a.nslots >>= 1;
+        a.Q = Q;
+        geometry(Q, &a.G, &a.nslots);
         a.n_tiles = (unsigned int)((h.n_members + a.nslots - 1) / a.nslots);
         // member rows in shared memory: pitch == 4 words (mod 32) so that 16-byte reads of the same element by
         // lanes of different members fall into different bank groups

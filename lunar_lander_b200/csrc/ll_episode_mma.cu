@@ -79,6 +79,12 @@ namespace
         unsigned int* queue;
         int p_dev;
         int w_off[LL_MAX_LAYERS], b_off[LL_MAX_LAYERS], out_pad[LL_MAX_LAYERS]; // the HBM row layout (ll_topo)
+        // small populations: a member's layouts are dealt to `chunks` warps (work item = member * chunks + chunk; chunk c flies the
+        // layouts at positions c, c + chunks, ... of the start order); partial sums meet in `part`, the last warp to arrive adds them
+        // in chunk order
+        int chunks;
+        double* part;             // [n_members][chunks][4] = fitness sum, steps, successes direction 0 / 1
+        unsigned int* part_count; // [n_members], zero before the launch
     };
 
     constexpr float LO_SCALE = 2048.f, LO_UNSCALE = 1.f / 2048.f;
@@ -234,7 +240,7 @@ namespace
         const int g      = lane >> 2, t = lane & 3;
         const int slot   = lane & 15; // lanes 16..31 mirror lanes 0..15
         const bool owner = lane < 16;
-        const int L      = a.n_layouts;
+        const int LT     = a.n_layouts; // row length of the per-episode outputs
 
         for (int i = lane; i < N::total; i += 32) sw[i] = 0.f; // k / out padding stays zero for the whole kernel
         __syncwarp();
@@ -244,7 +250,11 @@ namespace
             unsigned long long member = 0;
             if (lane == 0) member = (unsigned long long)atomicAdd(a.queue, 1u);
             member = __shfl_sync(0xffffffffu, member, 0);
-            if (member >= a.n_members) break;
+            const int C = a.chunks;
+            if (member >= a.n_members * (unsigned long long)C) break;
+            const int chunk = (int)(member % (unsigned long long)C);
+            member /= (unsigned long long)C;
+            const int L = (a.n_layouts - chunk + C - 1) / C; // layouts of this chunk: start-order positions chunk + i * C
             __syncwarp();
             stage_layer<N, 0>(a, a.params + member * (size_t)a.p_dev, sw, lane);
             __syncwarp();
@@ -260,7 +270,7 @@ namespace
             int next_layout = L < 16 ? L : 16;
             if (slot < L)
             {
-                layout                     = a.layouts[slot].next; // start order: longest expected flight first
+                layout                     = a.layouts[chunk + slot * C].next; // start order: longest expected flight first
                 const ll_layout<float> lay = a.layouts[layout];
                 dir                        = lay.dir;
                 cx = lay.center_x, lpad = lay.lpad_x1, lpad_r = lay.lpad_right;
@@ -328,13 +338,13 @@ namespace
                         if (a.ep_steps && owner)
                         {
                             const int meta = steps | (landed ? (1 << 28) : 0) | ((landed && !success) ? (1 << 29) : 0) | (success ? (1 << 30) : 0);
-                            a.ep_steps[member * (size_t)L + layout] = meta;
-                            a.ep_fit[member * (size_t)L + layout]   = fit;
+                            a.ep_steps[member * (size_t)LT + layout] = meta;
+                            a.ep_fit[member * (size_t)LT + layout]   = fit;
                         }
                         const int nl = next_layout + __popc(fin & ((1u << slot) - 1u));
                         if (nl < L)
                         { // reset(spad_x1, lpad_x1): src/game_logic.cpp:143-154
-                            layout                     = a.layouts[nl].next;
+                            layout                     = a.layouts[chunk + nl * C].next;
                             const ll_layout<float> lay = a.layouts[layout];
                             dir                        = lay.dir;
                             cx = lay.center_x, lpad = lay.lpad_x1, lpad_r = lay.lpad_right;
@@ -357,7 +367,24 @@ namespace
                 succ0 += __shfl_xor_sync(0xffffffffu, succ0, o);
                 succ1 += __shfl_xor_sync(0xffffffffu, succ1, o);
             }
-            if (lane == 0)
+            if (lane == 0 && C > 1)
+            { // hand the partial sums over; the last chunk of the member to arrive adds them in chunk order (deterministic)
+                double* mine = a.part + (member * (size_t)C + chunk) * 4;
+                mine[0] = fit_sum, mine[1] = (double)steps_sum, mine[2] = (double)succ0, mine[3] = (double)succ1;
+                __threadfence();
+                const unsigned int arrived = atomicAdd(a.part_count + member, 1u);
+                if (arrived == (unsigned int)C - 1u)
+                {
+                    __threadfence();
+                    const volatile double* all = a.part + member * (size_t)C * 4;
+                    double f = 0.0, st = 0.0, s0 = 0.0, s1 = 0.0;
+                    for (int c = 0; c < C; ++c) f += all[c * 4 + 0], st += all[c * 4 + 1], s0 += all[c * 4 + 2], s1 += all[c * 4 + 3];
+                    fit_sum = f, steps_sum = (unsigned int)st, succ0 = (unsigned int)s0, succ1 = (unsigned int)s1;
+                    a.part_count[member] = 0u;
+                }
+                else steps_sum = 0xffffffffu; // not the last: nothing to publish
+            }
+            if (lane == 0 && steps_sum != 0xffffffffu)
             {
                 float bonus0 = 0.f, bonus1 = 0.f;
                 for (unsigned i = 0; i < succ0; ++i) bonus0 += env.tp_landed_lr_bonus;
@@ -393,7 +420,28 @@ namespace
         if (warps < 1) return ll_fail(ctx, LL_EINVAL, "mma episode kernel: the member row does not fit in shared memory");
         const size_t smem = (size_t)warps * N::total * 4;
         LL_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        const unsigned long long ctas_needed = (h.n_members + warps - 1) / warps;
+        // a population smaller than the GPU's warp slots: deal each member's layouts to several warps so that they fly
+        // concurrently instead of in rounds of 16 (a generation then lasts one longest episode, not ceil(L / 16) of them)
+        const unsigned long long slots_w = (unsigned long long)ctx->sm_count * warps;
+        int chunks = 1;
+        if (h.n_members < slots_w) chunks = (int)std::max<unsigned long long>(1, std::min<unsigned long long>(slots_w / h.n_members, (unsigned long long)(h.n_layouts / 2)));
+        chunks = std::max(1, std::min(env_int("LL_MMA_CHUNKS", chunks), h.n_layouts));
+        a.chunks = chunks, a.part = nullptr, a.part_count = nullptr;
+        if (chunks > 1)
+        {
+            const size_t part_bytes = (size_t)h.n_members * chunks * 4 * sizeof(double), count_bytes = (size_t)h.n_members * sizeof(unsigned int);
+            if (ctx->part_cap < part_bytes + count_bytes)
+            {
+                if (ctx->d_part) cudaFree(ctx->d_part);
+                ctx->d_part = nullptr, ctx->part_cap = 0;
+                LL_CUDA(ctx, cudaMalloc(&ctx->d_part, part_bytes + count_bytes));
+                ctx->part_cap = part_bytes + count_bytes;
+            }
+            a.part       = static_cast<double*>(ctx->d_part);
+            a.part_count = reinterpret_cast<unsigned int*>(static_cast<char*>(ctx->d_part) + part_bytes);
+            LL_CUDA(ctx, cudaMemsetAsync(a.part_count, 0, count_bytes, ctx->stream));
+        }
+        const unsigned long long ctas_needed = (h.n_members * chunks + warps - 1) / warps;
         const unsigned int grid = (unsigned int)std::max<unsigned long long>(1, std::min<unsigned long long>((unsigned long long)ctx->sm_count, ctas_needed));
         ll_env<float> env;
         ll_make_env<float>(ctx->env_cfg, 1, &env);

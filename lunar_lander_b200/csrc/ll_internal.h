@@ -106,6 +106,8 @@ struct ll_ctx
     ll_step_rec* d_trace    = nullptr;
     int trace_cap = 0;
     void* d_scratch = nullptr; // small scratch (feedforward state, episode result)
+    void* d_part    = nullptr; // ll_episode_mma.cu: per-(member, chunk) partial sums + arrival counters (small populations)
+    size_t part_cap = 0;
     void* d_sim     = nullptr; // ll_sim.cu: the single stepped lander (state, view, penalties), allocated on first use
     bool sim_ready = false, sim_custom = false;
     double sim_lpad_x1 = 0.0, sim_init_x = 0.0;

@@ -118,8 +118,8 @@ def test_device_select_differs_only_in_tie_order(tmp_path, built):
     pick = lambda log, pat: re.findall(pat, log)
     for pat in (r"Best Avg Fitness: (\S+) \(Member (\d+)\)", r"Both Directions: (\d+)", r"--- (Generation \d+|Stagnation[^-]*) ---"):
         assert pick(r_our[1], pat) == pick(r_ref[1], pat) and pick(r_ref[1], pat)
-    mean_our = [float(x) for x in pick(r_our[1], r"Avg Fitness:\s+(\S+)")]
-    mean_ref = [float(x) for x in pick(r_ref[1], r"Avg Fitness:\s+(\S+)")]
+    mean_our = [float(x) for x in re.findall(r"^  Avg Fitness:\s+(\S+)", r_our[1], re.M)]
+    mean_ref = [float(x) for x in re.findall(r"^  Avg Fitness:\s+(\S+)", r_ref[1], re.M)]
     assert len(mean_our) == 6 and all(abs(a - b) <= 0.05 * abs(b) for a, b in zip(mean_our, mean_ref))
 
 

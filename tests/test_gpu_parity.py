@@ -96,6 +96,28 @@ def test_generation_bit_exact(ll, po, precision, n_layouts):
     eng.close()
 
 
+@pytest.mark.parametrize("precision", [64, 32])
+@pytest.mark.parametrize("q", [1, 2, 4, 8])
+@pytest.mark.parametrize("topo,n_layouts", [("8_16_32_16_8", 50), ("16_16", 5), ("32_128_32", 13)])
+def test_exact_kernel_lane_split_bit_exact(ll, po, precision, q, topo, n_layouts, monkeypatch):
+    """LL_EXACT_Q lanes per episode slot (the slot's output neurons dealt to Q lanes; chosen automatically for small populations):
+    a neuron's own arithmetic does not change, so every geometry must reproduce the oracle bit for bit."""
+    monkeypatch.setenv("LL_EXACT_Q", str(q))
+    pe, sizes = util.elite_population(topo, 13, 3)
+    members = np.concatenate([pe, util.random_population(sizes, 20, 11)])  # 33: ragged last tile
+    eng, cfg = _engine(ll, sizes, len(members), precision)
+    eng.set_members(0, members)
+    spad, lpad, d = util.layouts(50)
+    spad, lpad, d = spad[:n_layouts], lpad[:n_layouts], d[:n_layouts]
+    fit, lr, steps, st = eng.evaluate(spad, lpad, d, 1500)
+    want = po.evaluate(cfg.env_cfg(), sizes, 1, members.astype(eng.dtype), spad, lpad, d, 1500, precision, threads=8)
+    ep_steps, ep_flags, ep_fit = eng.read_episodes()
+    assert np.array_equal(ep_steps, want["ep_steps"]) and np.array_equal(ep_flags, want["ep_flags"])
+    assert np.array_equal(ep_fit, want["ep_fit"])
+    assert np.array_equal(steps, want["steps"]) and np.array_equal(lr, want["lr"]) and np.array_equal(fit, want["fitness"])
+    eng.close()
+
+
 @pytest.mark.parametrize("topo", ["16_16", "16_64_32", "32_128_32", "8_16_32_16_8"])
 def test_generation_topologies_and_golden(ll, po, topo):
     """Elites of the sample runs on the 50 balanced seed-5247 layouts: matches the fixtures produced by the
@@ -295,8 +317,11 @@ def test_weight_file_roundtrip(ll, po, tmp_path):
     g = a.index("generator")
     assert a[:g] == b[:g], "everything before the generator line is reproduced token for token"
     assert len(b) - b.index("generator") - 1 == 624
-    # the non-elite slots were regenerated from the elites with the stored epoch count as generation key
-    want = po.create_population(sizes, 5247, 100, 10, 500, 2, hdr["ratio"], True, True, 1.0, 0.1, np.concatenate([e, np.zeros((90, eng.P))]), 64)
+    # the non-elite slots were regenerated from the elites with the stored epoch count as generation key and the first word of
+    # the file's generator line as the GA key (for a file this library wrote that word is NNConfig.seed)
+    file_key = int(a[g + 1]) & 0xFFFFFFFF
+    assert int(b[b.index("generator") + 1]) == file_key, "a re-saved file keeps the key it was loaded with"
+    want = po.create_population(sizes, file_key, 100, 10, 500, 2, hdr["ratio"], True, True, 1.0, 0.1, np.concatenate([e, np.zeros((90, eng.P))]), 64)
     assert np.array_equal(eng.get_members(0, 100), want)
     eng.close()
 
@@ -372,6 +397,35 @@ def test_fast_tensor_core_kernel_tracks_exact_fp32(ll, po, topo, n_layouts, pop,
     assert rows.mean() >= 0.2
     rel = np.abs(ef[rows] - want["fitness"][rows]) / np.maximum(1.0, np.abs(want["fitness"][rows]))
     assert np.median(rel) <= 1e-5 and np.percentile(rel, 75) <= 1e-3, (np.median(rel), np.percentile(rel, 75), rel.max())
+
+
+def test_fast_small_population_layouts_dealt_to_several_warps(ll, po, monkeypatch):
+    """A population smaller than the GPU's warp slots: the tensor-core kernel deals each member's layouts to several warps
+    (LL_MMA_CHUNKS, automatic).  Episodes are flown by the same arithmetic whichever warp takes them: per-episode steps, flags
+    and fitness are identical to the one-warp-per-member run; member totals agree to summation order."""
+    members, sizes = util.elite_population("8_16_32_16_8", 37, 4, noise=0.02)
+    spad, lpad, d = util.layouts(50)
+    got = {}
+    for chunks in ("1", "3", "7", "25", ""):
+        if chunks:
+            monkeypatch.setenv("LL_MMA_CHUNKS", chunks)
+        else:
+            monkeypatch.delenv("LL_MMA_CHUNKS")
+        monkeypatch.setenv("LL_FAST_KERNEL", "mma")
+        eng, cfg = _engine(ll, sizes, len(members), 32, mode=1)
+        eng.set_members(0, members)
+        fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
+        got[chunks] = (fit, lr, steps) + tuple(eng.read_episodes())
+        # a second evaluation on the same context: the arrival counters were left at zero
+        fit2, lr2, steps2, _ = eng.evaluate(spad, lpad, d, 5000)
+        assert np.array_equal(fit, fit2) and np.array_equal(steps, steps2)
+        eng.close()
+    base = got["1"]
+    for chunks, g in got.items():
+        assert np.array_equal(g[3], base[3]) and np.array_equal(g[4], base[4]) and np.array_equal(g[5], base[5]), chunks
+        assert np.array_equal(g[2], base[2]) and np.array_equal(g[1], base[1]), chunks
+        assert np.allclose(g[0], base[0], rtol=1e-12, atol=1e-9), chunks
+        assert np.array_equal(g[2], g[3].sum(axis=1).astype(np.float64))
 
 
 @pytest.mark.parametrize("kernel", ["mma", "mmat"])
