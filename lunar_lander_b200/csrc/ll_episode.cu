@@ -51,6 +51,8 @@ namespace
         ll_episode_result* trace_result;
         // geometry
         int G, nslots;            // episode slots per member, members per warp tile
+        int chunks;               // warps a member's layouts are dealt to (chunk c flies layouts c, c + chunks, ...); > 1 needs ep_steps / ep_fit
+        unsigned int* part_count; // [n_members] arrival counters of the chunks, zero before the launch
         int Q;                    // lanes per episode slot (the slot's output neurons are dealt to its Q lanes); G * nslots * Q <= 32
         unsigned int n_tiles;
         int slot_stride;          // elements between member rows in shared memory
@@ -221,7 +223,11 @@ namespace
             unsigned int tile = 0;
             if (lane == 0) tile = atomicAdd(a.queue, 1u);
             tile = __shfl_sync(0xffffffffu, tile, 0);
-            if (tile >= a.n_tiles) break;
+            const int C = a.chunks;
+            if (tile >= a.n_tiles * (unsigned int)C) break;
+            const int chunk = (int)(tile % (unsigned int)C);
+            tile /= (unsigned int)C;
+            const int Lc = (L - chunk + C - 1) / C; // this chunk's layouts: chunk + i * C, i < Lc
             const unsigned long long m0 = (unsigned long long)tile * a.nslots;
             const int nvalid            = (int)min((unsigned long long)a.nslots, a.n_members - m0);
             const unsigned long long member = m0 + slot;
@@ -232,7 +238,7 @@ namespace
             __syncwarp();
             if (lane < nvalid)
                 ll_bulk_g2s(wsm + (size_t)lane * a.slot_stride, static_cast<const T*>(a.params) + (m0 + lane) * (size_t)tp.p_dev, row_bytes, bar);
-            if (j == 0 && sub == 0) next_layout[slot] = min(G, L);
+            if (j == 0 && sub == 0) next_layout[slot] = min(G, Lc);
             __syncwarp();
             ll_mbar_wait(bar, phase);
             phase ^= 1u;
@@ -248,12 +254,12 @@ namespace
                 x = lay.init_x, y = env.y0, vx = env.vx0, vy = env.vy0, fuel = env.max_fuel;
                 steps = 0, acc = 0.0;
             };
-            if (valid && j < L)
+            if (valid && j < Lc)
             {
-                begin_episode(j);
+                begin_episode(chunk + j * C);
                 active = true;
             }
-            const bool tracer = a.trace != nullptr && tile == 0 && lane == 0;
+            const bool tracer = a.trace != nullptr && tile == 0 && chunk == 0 && lane == 0;
 
             while (__any_sync(0xffffffffu, active))
             {
@@ -340,7 +346,7 @@ namespace
                         int nl = 0; // the slot's Q lanes hold identical state and arrive here together
                         if (sub == 0) nl = atomicAdd(&next_layout[slot], 1);
                         if (Q > 1) nl = __shfl_sync(gmask, nl, lane - sub);
-                        if (nl < L) begin_episode(nl);
+                        if (nl < Lc) begin_episode(chunk + nl * C);
                         else active = false;
                     }
                 }
@@ -348,15 +354,30 @@ namespace
             }
 
             // ---- per-member totals in layout order: src/nn_engine_trainer.cpp:518-530
+            if (C > 1) __threadfence(); // this lane's per-episode results are visible device-wide before the arrival is counted
             __syncwarp();
-            if (valid && j == 0 && sub == 0)
+            bool finalize = valid && j == 0 && sub == 0;
+            if (finalize && C > 1)
+            { // the member's other layouts were flown by other warps: the last chunk to arrive sums all of them, in layout order,
+              // from the per-episode arrays in global memory
+                __threadfence();
+                finalize = atomicAdd(a.part_count + member, 1u) == (unsigned int)C - 1u;
+                if (finalize)
+                {
+                    __threadfence();
+                    a.part_count[member] = 0u;
+                }
+            }
+            if (finalize)
             {
                 double total = 0.0, total_steps = 0.0;
                 T bonus0 = T(0), bonus1 = T(0);
+                const volatile int* g_meta   = a.ep_steps + member * (size_t)L;
+                const volatile double* g_fit = a.ep_fit + member * (size_t)L;
                 for (int l = 0; l < L; ++l)
                 {
-                    const int meta = res_meta[slot * L + l];
-                    total          = __dadd_rn(total, res_fit[slot * L + l]);
+                    const int meta = C > 1 ? g_meta[l] : res_meta[slot * L + l];
+                    total          = __dadd_rn(total, C > 1 ? g_fit[l] : res_fit[slot * L + l]);
                     total_steps    = __dadd_rn(total_steps, (double)(meta & 0x0fffffff));
                     if (meta & (1 << 30))
                     {
@@ -425,7 +446,39 @@ namespace
             }
         }
         a.Q = Q;
-        geometry(Q, &a.G, &a.nslots);
+        // a member with more layouts than a warp has lanes needs several rounds; when the population is too small to fill the GPU
+        // anyway, its layouts are dealt to ceil(L / 32) warps instead (one episode per lane, one round)
+        int chunks = 1;
+        {
+            int g = 0, n = 0;
+            if (h.trace == nullptr && h.ep_steps && h.ep_fit && L > 32 / Q && geometry(Q, &g, &n) < (unsigned long long)ctx->sm_count * 8ull)
+                chunks = (L + 32 / Q - 1) / (32 / Q);
+            const char* force = getenv("LL_EXACT_CHUNKS");
+            if (force && *force && h.trace == nullptr && h.ep_steps && h.ep_fit) chunks = std::max(1, std::min(atoi(force), L));
+        }
+        a.chunks = chunks, a.part_count = nullptr;
+        const int L_eff = (L + chunks - 1) / chunks; // layouts per chunk (the geometry is sized for these)
+        {
+            const int E = 32 / Q;
+            int G       = 1;
+            while (G < L_eff && G < E) G <<= 1;
+            int nslots = E / G;
+            while (nslots > 1 && (size_t)nslots * tp.p_dev * sizeof(T) > (size_t)48 << 10) nslots >>= 1;
+            a.G = G, a.nslots = nslots;
+        }
+        if (chunks > 1)
+        {
+            const size_t count_bytes = (size_t)h.n_members * sizeof(unsigned int);
+            if (ctx->part_cap < count_bytes)
+            {
+                if (ctx->d_part) cudaFree(ctx->d_part);
+                ctx->d_part = nullptr, ctx->part_cap = 0;
+                LL_CUDA(ctx, cudaMalloc(&ctx->d_part, count_bytes));
+                ctx->part_cap = count_bytes;
+            }
+            a.part_count = static_cast<unsigned int*>(ctx->d_part);
+            LL_CUDA(ctx, cudaMemsetAsync(a.part_count, 0, count_bytes, ctx->stream));
+        }
         a.n_tiles = (unsigned int)((h.n_members + a.nslots - 1) / a.nslots);
         // member rows in shared memory: pitch == 4 words (mod 32) so that 16-byte reads of the same element by
         // lanes of different members fall into different bank groups
@@ -436,7 +489,7 @@ namespace
         a.off_w       = 256;
         a.off_act     = up(a.off_w + a.nslots * a.slot_stride * (int)sizeof(T));
         a.off_fit     = up(a.off_act + 2 * tp.max_width * 32 * (int)sizeof(T));
-        const int R   = L > 32 ? L : 32;
+        const int R   = std::max(32, a.nslots * L); // per-layout results of every member of the tile (indexed slot * L + layout)
         a.off_meta    = a.off_fit + R * 8;
         a.warp_bytes  = up(a.off_meta + R * 4);
 
@@ -452,7 +505,7 @@ namespace
         int per_sm = 0;
         LL_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, wpb * 32, smem));
         if (per_sm < 1) return ll_fail(ctx, LL_EINVAL, "episode kernel does not fit on an SM");
-        unsigned int blocks_needed = (a.n_tiles + wpb - 1) / wpb;
+        unsigned int blocks_needed = (a.n_tiles * (unsigned int)chunks + wpb - 1) / wpb;
         unsigned int grid          = (unsigned int)(per_sm * ctx->sm_count);
         if (grid > blocks_needed) grid = blocks_needed;
         if (grid < 1) grid = 1;

@@ -223,11 +223,12 @@ namespace
     }
 
     // warps per CTA (one CTA per SM): one member buffer each within 227 KB of shared memory, a multiple of four so that the
-    // four sub-partitions carry the same load, at most 8 (one warp per sub-partition already saturates its issue port)
+    // four sub-partitions carry the same load, at most 16 (the small networks leave the issue slots half empty with two warps per
+    // sub-partition: ncu 44 % issue-active on configs[2]; their register count allows 12 - 16 resident warps)
     template <class N> constexpr int max_warps()
     {
         const int by_smem = (227 * 1024) / (N::total * 4);
-        return by_smem >= 8 ? 8 : (by_smem >= 4 ? 4 : (by_smem < 1 ? 1 : by_smem));
+        return by_smem >= 16 ? 16 : (by_smem >= 12 ? 12 : (by_smem >= 8 ? 8 : (by_smem >= 4 ? 4 : (by_smem < 1 ? 1 : by_smem))));
     }
 
     template <class N, int EXP = 0>

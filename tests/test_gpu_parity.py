@@ -118,6 +118,27 @@ def test_exact_kernel_lane_split_bit_exact(ll, po, precision, q, topo, n_layouts
     eng.close()
 
 
+@pytest.mark.parametrize("precision", [64, 32])
+@pytest.mark.parametrize("chunks", ["", "1", "2", "5"])
+def test_exact_kernel_layout_chunks_bit_exact(ll, po, precision, chunks, monkeypatch):
+    """Small population, 50 layouts: the exact kernel deals a member's layouts to ceil(50 / 32) = 2 warps (LL_EXACT_CHUNKS forces a
+    count) and the last warp to arrive sums all 50 results in layout order: still the oracle's bits, on repeated evaluations too."""
+    if chunks:
+        monkeypatch.setenv("LL_EXACT_CHUNKS", chunks)
+    pe, sizes = util.elite_population("16_16", 20, 3)
+    members = np.concatenate([pe, util.random_population(sizes, 17, 11)])
+    eng, cfg = _engine(ll, sizes, len(members), precision)
+    eng.set_members(0, members)
+    spad, lpad, d = util.layouts(50)
+    want = po.evaluate(cfg.env_cfg(), sizes, 1, members.astype(eng.dtype), spad, lpad, d, 2000, precision, threads=8)
+    for _ in range(2):
+        fit, lr, steps, st = eng.evaluate(spad, lpad, d, 2000)
+        ep_steps, ep_flags, ep_fit = eng.read_episodes()
+        assert np.array_equal(ep_steps, want["ep_steps"]) and np.array_equal(ep_fit, want["ep_fit"])
+        assert np.array_equal(steps, want["steps"]) and np.array_equal(lr, want["lr"]) and np.array_equal(fit, want["fitness"])
+    eng.close()
+
+
 @pytest.mark.parametrize("topo", ["16_16", "16_64_32", "32_128_32", "8_16_32_16_8"])
 def test_generation_topologies_and_golden(ll, po, topo):
     """Elites of the sample runs on the 50 balanced seed-5247 layouts: matches the fixtures produced by the
