@@ -222,13 +222,14 @@ namespace
         if constexpr (L + 1 < N::NL) stage_layer<N, L + 1>(a, row, sw, lane);
     }
 
-    // warps per CTA (one CTA per SM): one member buffer each within 227 KB of shared memory, a multiple of four so that the
-    // four sub-partitions carry the same load, at most 16 (the small networks leave the issue slots half empty with two warps per
-    // sub-partition: ncu 44 % issue-active on configs[2]; their register count allows 12 - 16 resident warps)
+    // warps per CTA (one CTA per SM): one member buffer each within 227 KB of shared memory - as many as fit up to 8, then 12 or 16
+    // for the small networks.  Measured on configs[3] (32_128_32, 37.4 KB per member): 6 warps reach 97.9 % of the FP32 FMA roofline
+    // against 84.4 % with 4 - the second warp of a sub-partition fills the issue slots the first leaves while it waits on its own
+    // HMMA -> epilogue -> HMMA chain, which outweighs the uneven 2-2-1-1 split; configs[2]: 12 warps 54.4 % against 47.1 % with 8.
     template <class N> constexpr int max_warps()
     {
         const int by_smem = (227 * 1024) / (N::total * 4);
-        return by_smem >= 16 ? 16 : (by_smem >= 12 ? 12 : (by_smem >= 8 ? 8 : (by_smem >= 4 ? 4 : (by_smem < 1 ? 1 : by_smem))));
+        return by_smem >= 16 ? 16 : (by_smem >= 12 ? 12 : (by_smem >= 8 ? 8 : (by_smem < 1 ? 1 : by_smem)));
     }
 
     template <class N, int EXP = 0>
