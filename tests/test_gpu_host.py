@@ -156,3 +156,23 @@ def test_step_checkpoint_name_quirk_and_bad_arguments(tmp_path, built):
     assert rc == 1 and "requires an integer argument" in err
     rc, out, err = run(os.path.join(BIN, "main_train_d"), str(tmp_path))  # no config.txt there
     assert rc == 1 and "FATAL: Could not load configuration" in err
+
+
+def test_python_sharded_trainer_prints_the_cpp_trainer_log(tmp_path, built):
+    """lunar_lander_b200.trainer (the multi-GPU trainer: one process per GPU over torch.distributed, here with one process) against
+    host/bin/main_train_d with GpuCfg.select = device: same generations, same best members and fitness, same files."""
+    import sys
+    ov = dict(SMALL)
+    ov.update({"NNConfig.hlayers": "8,16,8", "NNConfig.epochs": 7, "NNConfig.population_size": 80})
+    a, b = str(tmp_path / "cpp"), str(tmp_path / "py")
+    write_config(a, **ov)
+    write_config(b, **ov)
+    r_cpp = run(os.path.join(BIN, "main_train_d"), a, "--set", "GpuCfg.select=device")
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    p = subprocess.run([sys.executable, "-m", "lunar_lander_b200.trainer"], cwd=b, capture_output=True, text=True, timeout=600, env=env)
+    assert r_cpp[0] == 0 and p.returncode == 0, (r_cpp[2], p.stderr)
+    assert normalise(p.stdout) == normalise(r_cpp[1])
+    files = sorted(os.listdir(os.path.join(a, "data")))
+    assert files == sorted(os.listdir(os.path.join(b, "data"))) and "lunar_lander_last.txt" in files
+    for name in files:
+        assert open(os.path.join(a, "data", name)).read() == open(os.path.join(b, "data", name)).read(), name
