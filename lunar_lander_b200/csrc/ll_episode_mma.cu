@@ -229,7 +229,7 @@ namespace
     template <class N> constexpr int max_warps()
     {
         const int by_smem = (227 * 1024) / (N::total * 4);
-        return by_smem >= 16 ? 16 : (by_smem >= 12 ? 12 : (by_smem >= 8 ? 8 : (by_smem < 1 ? 1 : by_smem)));
+        return by_smem >= 16 ? 16 : (by_smem >= 12 ? 12 : (by_smem < 1 ? 1 : by_smem));
     }
 
     template <class N, int EXP = 0>

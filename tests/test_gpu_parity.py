@@ -449,6 +449,33 @@ def test_fast_small_population_layouts_dealt_to_several_warps(ll, po, monkeypatc
         assert np.array_equal(g[2], g[3].sum(axis=1).astype(np.float64))
 
 
+@pytest.mark.parametrize("topo,n_layouts,pop", [("16_64_32", 8, 333), ("8_16_8", 1, 500), ("8_16_32_16_8", 5, 97), ("32_128_32", 8, 61)])
+def test_fast_several_members_per_warp(ll, po, topo, n_layouts, pop, monkeypatch):
+    """Up to 8 layouts: the transposed tensor-core kernel can fly LL_MMAT_MEMBERS members per warp, one 8-slot tile each (lane = slot
+    for the environment, tiles refilled from the queue independently).  Every episode goes through the same products and the same
+    environment code as with one member per warp: per-episode steps, flags and fitness are identical; member totals agree to
+    summation order."""
+    members, sizes = util.elite_population(topo, pop, 4, noise=0.02)
+    members[pop // 2:] += util.random_population(sizes, pop - pop // 2, 8, scale=0.05)
+    spad, lpad, d = util.layouts(50)
+    spad, lpad, d = spad[:n_layouts], lpad[:n_layouts], d[:n_layouts]
+    monkeypatch.setenv("LL_FAST_KERNEL", "mmat")
+    got = {}
+    for nm in ("0", "2", "3", "4"):
+        monkeypatch.setenv("LL_MMAT_MEMBERS", nm)
+        eng, cfg = _engine(ll, sizes, pop, 32, mode=1)
+        eng.set_members(0, members)
+        fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
+        assert "_mmat_" in eng.info.kernel.decode()
+        got[nm] = (fit, lr, steps) + tuple(eng.read_episodes())
+        eng.close()
+    base = got["0"]
+    for nm, r in got.items():
+        assert np.array_equal(r[3], base[3]) and np.array_equal(r[4], base[4]) and np.array_equal(r[5], base[5]), nm
+        assert np.array_equal(r[2], base[2]) and np.array_equal(r[1], base[1]), nm
+        assert np.allclose(r[0], base[0], rtol=1e-12, atol=1e-9), nm
+
+
 @pytest.mark.parametrize("kernel", ["mma", "mmat"])
 def test_fast_mode_constant_policies(ll, kernel, monkeypatch):
     """Constant-action networks do not depend on the forward arithmetic: the fast kernel must reproduce the reference-owned
