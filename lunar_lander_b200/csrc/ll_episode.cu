@@ -56,6 +56,7 @@ namespace
         int Q;                    // lanes per episode slot (the slot's output neurons are dealt to its Q lanes); G * nslots * Q <= 32
         unsigned int n_tiles;
         int slot_stride;          // elements between member rows in shared memory
+        int width_a, width_b;     // rows of the two activation buffers: a0 holds the inputs and the outputs of the odd layers, a1 the even ones
         int off_w, off_act, off_fit, off_meta, warp_bytes; // byte offsets inside a warp's shared-memory slice
     };
 
@@ -203,7 +204,7 @@ namespace
         T* wsm            = reinterpret_cast<T*>(ws + a.off_w);
         const int Q = a.Q, sub = lane % Q, elane = lane / Q; // Q lanes share one episode slot (and its activation column)
         T* act0           = reinterpret_cast<T*>(ws + a.off_act) + (lane - sub);
-        T* act1           = act0 + tp.max_width * 32;
+        T* act1           = act0 + a.width_a * 32;
         double* res_fit   = reinterpret_cast<double*>(ws + a.off_fit);
         int* res_meta     = reinterpret_cast<int*>(ws + a.off_meta);
 
@@ -488,7 +489,16 @@ namespace
         auto up       = [](int v) { return (v + 127) & ~127; };
         a.off_w       = 256;
         a.off_act     = up(a.off_w + a.nslots * a.slot_stride * (int)sizeof(T));
-        a.off_fit     = up(a.off_act + 2 * tp.max_width * 32 * (int)sizeof(T));
+        // the two activation buffers alternate layer by layer: each is as wide as the widest vector it ever holds (5-32-128-32-4:
+        // 128 + 32 rows instead of 2 x 128 - with a 69 KB fp64 row that is the difference between one and two warps per SM)
+        a.width_a = tp.in[0], a.width_b = 8;
+        for (int l = 0; l < tp.n_layers; ++l)
+        {
+            int& w = (l & 1) ? a.width_a : a.width_b;
+            w      = std::max(w, tp.out_pad[l]);
+        }
+        a.width_a = std::max(a.width_a, 8);
+        a.off_fit = up(a.off_act + (a.width_a + a.width_b) * 32 * (int)sizeof(T));
         const int R   = std::max(32, a.nslots * L); // per-layout results of every member of the tile (indexed slot * L + layout)
         a.off_meta    = a.off_fit + R * 8;
         a.warp_bytes  = up(a.off_meta + R * 4);

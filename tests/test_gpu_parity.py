@@ -347,6 +347,54 @@ def test_weight_file_roundtrip(ll, po, tmp_path):
     eng.close()
 
 
+@pytest.mark.parametrize("precision", [64, 32])
+@pytest.mark.parametrize("pop,n_layouts,max_steps", [(1, 1, 5000), (1, 50, 700), (3, 130, 400), (5, 7, 1), (2, 33, 2), (64, 1, 9)])
+def test_edge_geometries_bit_exact(ll, po, precision, pop, n_layouts, max_steps):
+    """Degenerate and ragged shapes through the exact kernel: a single member, a single layout, more layouts than four warps
+    have lanes (130: dealt to 5 warps), episodes cut after one or two steps (the first step has no landing test,
+    src/game_logic.cpp:199), a population smaller than one warp tile."""
+    pe, sizes = util.elite_population("8_16_8", max(pop, 2), 3)
+    members = pe[:pop]
+    rng = np.random.default_rng(7)
+    spad = rng.integers(10, 870, n_layouts).astype(np.int32)
+    lpad = rng.integers(10, 750, n_layouts).astype(np.int32)
+    d = (spad + 40 >= lpad + 100).astype(np.uint64)
+    eng, cfg = _engine(ll, sizes, pop, precision, top=1)
+    eng.set_members(0, members)
+    fit, lr, steps, st = eng.evaluate(spad, lpad, d, max_steps)
+    want = po.evaluate(cfg.env_cfg(), sizes, 1, members.astype(eng.dtype), spad, lpad, d, max_steps, precision, threads=2)
+    ep_steps, ep_flags, ep_fit = eng.read_episodes()
+    assert np.array_equal(ep_steps, want["ep_steps"]) and np.array_equal(ep_flags, want["ep_flags"]) and np.array_equal(ep_fit, want["ep_fit"])
+    assert np.array_equal(steps, want["steps"]) and np.array_equal(lr, want["lr"]) and np.array_equal(fit, want["fitness"])
+    assert ep_steps.max() <= max_steps and st.members == pop
+    elites = eng.select(None)
+    assert list(elites) == list(po.topk(want["fitness"], 1))
+    eng.close()
+
+
+@pytest.mark.parametrize("kernel", ["mma", "mmat", "ffma"])
+@pytest.mark.parametrize("pop,n_layouts,max_steps", [(1, 1, 5000), (3, 130, 400), (5, 7, 1), (2, 33, 2), (70, 9, 300)])
+def test_edge_geometries_fast(ll, po, kernel, pop, n_layouts, max_steps, monkeypatch):
+    """The same shapes through the three fast kernels: every episode is flown exactly once (step counts of the constant-action
+    members are the oracle's, totals are consistent), nothing is lost or double-booked at tile / chunk boundaries."""
+    sizes = util.TOPOLOGIES["16_16"]
+    members = np.stack([util.constant_action_member(sizes, a % 4) for a in range(pop)])
+    rng = np.random.default_rng(11)
+    spad = rng.integers(10, 870, n_layouts).astype(np.int32)
+    lpad = rng.integers(10, 750, n_layouts).astype(np.int32)
+    d = (spad + 40 >= lpad + 100).astype(np.uint64)
+    monkeypatch.setenv("LL_FAST_KERNEL", kernel)
+    eng, cfg = _engine(ll, sizes, pop, 32, mode=1, top=1)
+    eng.set_members(0, members)
+    fit, lr, steps, st = eng.evaluate(spad, lpad, d, max_steps)
+    want = po.evaluate(cfg.env_cfg(), sizes, 1, members.astype(np.float32), spad, lpad, d, max_steps, 32, threads=2)
+    ep_steps, ep_flags, ep_fit = eng.read_episodes()
+    assert np.array_equal(ep_steps, want["ep_steps"]) and np.array_equal(ep_flags, want["ep_flags"])
+    assert np.array_equal(steps, want["steps"]) and np.array_equal(lr, want["lr"])
+    assert np.allclose(ep_fit, want["ep_fit"], rtol=3e-4, atol=1e-3) and np.allclose(fit, want["fitness"], rtol=3e-4, atol=1e-2)
+    eng.close()
+
+
 # 7. fast fp32 mode: judged on outcomes, not sequences
 @pytest.mark.parametrize("topo,n_layouts,pop", [("16_64_32", 50, 256), ("32_128_32", 50, 96), ("16_64_32", 8, 512), ("8_16_8", 33, 300),
                                                 ("16_16", 5, 777), ("8_16_32_16_8", 50, 64), ("16_16", 1, 2048)])
