@@ -421,10 +421,9 @@ namespace
         a.trace = h.trace, a.trace_cap = h.trace_cap, a.trace_result = h.trace_result;
         const int L = h.n_layouts;
         // Geometry of a warp tile: Q lanes per episode slot, G slots per member, nslots members.  Q = 1 (a lane walks all neurons of
-        // its episode) is the default.  LL_EXACT_Q = 2 | 4 | 8 deals a slot's output neurons to Q lanes; it is bit-identical (tested)
-        // but, measured on B200, SLOWER for the small populations it was meant for (configs[0], 100 x 50: 148 / 168 / 197 / 372 ms per
-        // generation for Q = 1 / 2 / 4 / 8): a generation lasts as long as its longest lane's chain of dependent fp64 operations, and
-        // with fewer slots per warp a member's layouts need more sequential rounds.  Kept as an experiment switch only.
+        // its episode) unless lanes would idle (below).  Forcing Q > 1 on a SMALL population to get more warps does not pay
+        // (configs[0], 100 x 50: 148 / 168 / 197 / 372 ms per generation for Q = 1 / 2 / 4 / 8): a generation lasts as long as its longest
+        // lane's chain of dependent fp64 operations, and fewer slots per warp mean more sequential rounds.  LL_EXACT_Q forces a value.
         auto geometry = [&](int q, int* g_out, int* nslots_out) {
             const int E = 32 / q;
             int G       = 1;
@@ -439,6 +438,14 @@ namespace
         int Q = 1;
         if (h.trace == nullptr)
         {
+            // few layouts and a wide network: the 48 KB staging cap leaves lane groups without a member (16_64_32 fp64 with 8
+            // layouts: 8 busy lanes of 32) - give the idle lanes to the busy slots, Q lanes per slot, as far as the widest layer has
+            // tiles of 4 neurons to deal.  The number of slots per member does not change, so no extra rounds.
+            int g1 = 0, n1 = 0;
+            geometry(1, &g1, &n1);
+            int widest = 4;
+            for (int l = 0; l < tp.n_layers; ++l) widest = std::max(widest, tp.out_pad[l]);
+            while (Q * 2 * g1 * n1 <= 32 && Q * 2 <= widest / 4 && Q < 8) Q <<= 1;
             const char* force = getenv("LL_EXACT_Q");
             if (force && *force)
             {

@@ -13,6 +13,6 @@ for l in open("$O/j36_$name.log"):
         d = json.loads(l); print("$name", "%.4g" % d["value"], "%.4f" % d["roofline"]["frac"], "%.2f ms" % d["ms_per_step"], d["config"]["kernel"])
 P
 }
-run c4_f64 --workload c4 --precision 64 --exact --pop-per-gpu 8192
-run c4_f32x --workload c4 --exact --pop-per-gpu 8192
+
+LL_EXACT_Q=1 run c3_f64_q1 --workload c3 --precision 64 --exact --pop-per-gpu 16384
 run c3_f64 --workload c3 --precision 64 --exact --pop-per-gpu 16384
