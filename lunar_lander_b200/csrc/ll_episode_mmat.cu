@@ -26,6 +26,10 @@
 
 #include "ll_env.cuh"
 
+#ifndef LL_MMAT_PANEL
+#define LL_MMAT_PANEL 8 /* accumulator tiles (x3 split products) alive at once */
+#endif
+
 #ifndef LL_MMAT_MEMBERS_DEFAULT
 #define LL_MMAT_MEMBERS_DEFAULT 0
 #endif
@@ -44,14 +48,19 @@ namespace
         static __host__ __device__ constexpr int k16(int l) { return (sz(l) + 15) & ~15; }
         static __host__ __device__ constexpr int m16(int l) { return (sz(l + 1) + 15) & ~15; }
         // shared-memory layout in 32-bit words: per layer the A fragments [m16/16][k16/16][hi, lo][32 lanes][4 words] (one word per
-        // weight), then the bias [m16/16][8 (g)][2] = {b[16mt + g], b[16mt + g + 8]}
+        // weight), then the bias [m16/16][8 (g)][2] = {b[16mt + g], b[16mt + g + 8]}.  Two layers keep half fragments: the first has
+        // at most 8 inputs (k 8..15 of its only k tile is padding: words a2, a3 are zero and not stored), the last at most 8 outputs
+        // (rows 8..15 of its only output tile: a1, a3).  For 16_64_32 that is 14.3 instead of 15.9 KB per member: 15 warps per SM.
+        static __host__ __device__ constexpr bool half_k(int l) { return NL > 1 && l == 0 && sz(0) <= 8; }
+        static __host__ __device__ constexpr bool half_m(int l) { return NL > 1 && l == NL - 1 && sz(NL) <= 8; }
+        static __host__ __device__ constexpr int w_words(int l) { return (half_k(l) || half_m(l)) ? m16(l) * k16(l) / 2 : m16(l) * k16(l); }
         static __host__ __device__ constexpr int w_off(int l)
         {
             int o = 0;
-            for (int i = 0; i < l; ++i) o += m16(i) * k16(i) + m16(i);
+            for (int i = 0; i < l; ++i) o += w_words(i) + m16(i);
             return o;
         }
-        static __host__ __device__ constexpr int b_off(int l) { return w_off(l) + m16(l) * k16(l); }
+        static __host__ __device__ constexpr int b_off(int l) { return w_off(l) + w_words(l); }
         static constexpr int total = w_off(NL);
         static __host__ __device__ constexpr bool ok() { return sz(0) <= 8 && sz(NL) <= 8; }
     };
@@ -96,6 +105,22 @@ namespace
         lo = *reinterpret_cast<const uint32_t*>(&pl);
     }
 
+    // A fragment (hi: hl = 0, scaled lo: hl = 1) of tile (mt, kt) of layer L from a staged row
+    template <class N, int L> __device__ __forceinline__ uint4 load_w(const float* __restrict__ row, int lane, int tile, int hl)
+    {
+        if constexpr (N::half_k(L))
+        {
+            const uint2 v = reinterpret_cast<const uint2*>(row + N::w_off(L))[(tile * 2 + hl) * 32 + lane];
+            return make_uint4(v.x, v.y, 0u, 0u);
+        }
+        else if constexpr (N::half_m(L))
+        {
+            const uint2 v = reinterpret_cast<const uint2*>(row + N::w_off(L))[(tile * 2 + hl) * 32 + lane];
+            return make_uint4(v.x, 0u, v.y, 0u);
+        }
+        else return reinterpret_cast<const uint4*>(row + N::w_off(L))[(tile * 2 + hl) * 32 + lane];
+    }
+
     // One layer for the warp's NT slot tiles.  xh/xl[j][kt][2]: B fragments (hi / lo) of slot tile j, k tile kt.  Output: the next
     // layer's B fragments yh/yl[j][mt][2] (tanh applied, split, transposed), or for the output layer z[j][2] = tanh'd outputs
     // (row g, slots 2t and 2t+1).  Output tiles go in panels of PM so that the 3 * PM * NT accumulator tiles stay in registers.
@@ -105,11 +130,10 @@ namespace
                                             uint32_t (&yl)[NT][N::m16(L) / 16][2], float (&z)[NT][2])
     {
         constexpr int KT = N::k16(L) / 16, MT = N::m16(L) / 16;
-        constexpr int PMAX = 8 / NT;
+        constexpr int PMAX = LL_MMAT_PANEL / NT;
         constexpr int PM   = MT >= PMAX ? PMAX : MT;
         constexpr bool LAST = L == N::NL - 1;
         static_assert(MT % PM == 0, "output tiles must fill whole panels");
-        const uint4* W  = reinterpret_cast<const uint4*>(sw + N::w_off(L)) + lane;
         const float2* B = reinterpret_cast<const float2*>(sw + N::b_off(L)) + g;
 #pragma unroll
         for (int mp = 0; mp < MT; mp += PM)
@@ -132,8 +156,8 @@ namespace
 #pragma unroll
                 for (int i = 0; i < PM; ++i)
                 {
-                    const uint4 wh = W[(((mp + i) * KT + kt) * 2 + 0) * 32];
-                    const uint4 wl = W[(((mp + i) * KT + kt) * 2 + 1) * 32];
+                    const uint4 wh = load_w<N, L>(sw, lane, (mp + i) * KT + kt, 0);
+                    const uint4 wl = load_w<N, L>(sw, lane, (mp + i) * KT + kt, 1);
 #pragma unroll
                     for (int j = 0; j < NT; ++j)
                     {
@@ -202,11 +226,12 @@ namespace
                     const __half lo = __float2half_rn(fminf(fmaxf((e[q] - __half2float(hi)) * T_LO_SCALE, -65504.f), 65504.f));
                     const int r = o & 15, c = k & 15;
                     const int tile = (o >> 4) * KT + (k >> 4);
-                    const int word = (r >> 3) + 2 * (c >> 3);
                     const int ln   = (r & 7) * 4 + ((c & 7) >> 1);
-                    const int base = ((tile * 2) * 32 + ln) * 4 + word; // hi fragment; the lo fragment is 128 words further
-                    dst[base * 2 + (c & 1)]         = hi;
-                    dst[(base + 128) * 2 + (c & 1)] = lo;
+                    constexpr int FW = (N::half_k(L) || N::half_m(L)) ? 2 : 4; // words per lane in a fragment
+                    const int word = N::half_k(L) ? (r >> 3) : (N::half_m(L) ? (c >> 3) : (r >> 3) + 2 * (c >> 3));
+                    const int base = ((tile * 2) * 32 + ln) * FW + word; // hi fragment; the lo fragment is 32 * FW words further
+                    dst[base * 2 + (c & 1)]             = hi;
+                    dst[(base + 32 * FW) * 2 + (c & 1)] = lo;
                 }
             }
         }
@@ -218,14 +243,17 @@ namespace
         if constexpr (L + 1 < N::NL) stage_t<N, L + 1>(a, row, sw, lane);
     }
 
-    template <class N> constexpr int t_max_warps()
+    // warps per CTA (one CTA per SM): as many member rows as fit in 227 KB of shared memory, at most 16.  With one slot tile per warp
+    // the register count (<= 160) never limits this; with two tiles (up to 255 registers) the count stays at 12 / 8 / what fits.
+    template <class N, int NT> constexpr int t_max_warps()
     {
         const int by_smem = (227 * 1024) / (N::total * 4);
-        return by_smem >= 16 ? 16 : (by_smem >= 12 ? 12 : (by_smem < 1 ? 1 : by_smem));
+        if (NT == 1) return by_smem >= 16 ? 16 : (by_smem < 1 ? 1 : by_smem);
+        return by_smem >= 12 ? 12 : (by_smem >= 8 ? 8 : (by_smem < 1 ? 1 : by_smem)); // two tiles per warp need > 128 registers
     }
 
     template <class N, int NT>
-    __global__ void __launch_bounds__(32 * t_max_warps<N>(), 1) ll_episode_mmat_kernel(const __grid_constant__ ll_env<float> env, const __grid_constant__ mmat_args a)
+    __global__ void __launch_bounds__(32 * t_max_warps<N, NT>(), 1) ll_episode_mmat_kernel(const __grid_constant__ ll_env<float> env, const __grid_constant__ mmat_args a)
     {
         static_assert(N::ok(), "topology not supported by the mma episode kernel");
         extern __shared__ __align__(16) float smem_all[];
@@ -438,7 +466,7 @@ namespace
         auto kern = ll_episode_mmat_kernel<N, NT>;
         int max_smem = 0;
         LL_CUDA(ctx, cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device));
-        int warps = std::min<int>(t_max_warps<N>(), max_smem / (N::total * 4));
+        int warps = std::min<int>(t_max_warps<N, NT>(), max_smem / (N::total * 4));
         warps     = std::min(warps, t_env_int("LL_MMA_WARPS_PER_SM", warps));
         if (warps < 1) return ll_fail(ctx, LL_EINVAL, "mmat episode kernel: the member row does not fit in shared memory");
         const size_t smem = (size_t)warps * N::total * 4;
