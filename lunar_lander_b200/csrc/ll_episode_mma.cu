@@ -10,11 +10,11 @@
 //   * the 16 slots are the M dimension of mma.sync.m16n8k16 (f16 operands, fp32 accumulate).  The activations never leave
 //     the register file: the C fragment of layer l (rows g / g+8, columns 8nt+2t, 8nt+2t+1) packed to half2 IS register
 //     (nt & 1) * 2 + {0, 1} of the A fragment of k block nt / 2 of layer l+1;
-//   * fp32 accuracy from 11-bit operands: x = hi + lo with hi = the leading 11 significant bits and lo = x - hi (weights:
-//     lo scaled by 2^11 so that it stays in fp16's normal range); D = A_hi*B_hi + A_lo*B_hi + 2^-11 A_hi*B_lo', B_lo' = 2^11 B_lo; the
-//     dropped lo*lo term is < 2^-21 relative (measured: the share of episodes whose step count equals the exact fp32
-//     path's is the same 0.978 as for the FFMA kernel; dropping A_lo*B_hi as well lowers it to 0.50).  The three terms
-//     accumulate in three separate register tiles (a dependent HMMA would wait 21 cycles for its predecessor);
+//   * fp32 accuracy from 11-bit operands: x = hi + lo with hi = the leading 11 significant bits and lo = x - hi, both fp16 and
+//     unscaled (|lo| < 2^-11 |x|; where lo is an fp16 subnormal its absolute error is <= 2^-25: activations are <= 5, weights that
+//     small contribute below fp32 resolution of a pre-activation).  D = bias + A_hi*B_hi + A_lo*B_hi + A_hi*B_lo in one fp32
+//     accumulator tile; the dropped lo*lo term is < 2^-21 relative (measured: the share of episodes whose step count equals the
+//     exact fp32 path's is the same 0.978 as for the FFMA kernel; dropping A_lo*B_hi as well lowers it to 0.50);
 //   * the member's weights are split ONCE per member, while they are staged into shared memory, and stored as ready-made
 //     B fragments {b0_hi, b1_hi, b0_lo, b1_lo} per (output block, k block, lane): one conflict-free LDS.128 per three
 //     HMMAs, 4 bytes per weight (35.3 KB for 32_128_32);
@@ -87,8 +87,6 @@ namespace
         unsigned int* part_count; // [n_members], zero before the launch
     };
 
-    constexpr float LO_SCALE = 2048.f, LO_UNSCALE = 1.f / 2048.f;
-
     __device__ __forceinline__ void mma_f16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1)
     {
         asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
@@ -109,9 +107,9 @@ namespace
         lo = *reinterpret_cast<const uint32_t*>(&pl);
     }
 
-    // One layer for the warp's 16 slots.  ah/al[kt][4]: A fragments (hi / scaled lo) of k block kt (16 inputs).  Output:
+    // One layer for the warp's 16 slots.  ah/al[kt][4]: A fragments (hi / lo) of k block kt (16 inputs).  Output:
     // the next layer's A fragments nh/nl (tanh applied, split, packed), or for the output layer the raw fragment z[4]
-    // (rows g / g+8, outputs 2t, 2t+1) with tanh applied.  Output blocks go in panels of PN <= 8 so that the 3 * PN
+    // (rows g / g+8, outputs 2t, 2t+1) with tanh applied.  Output blocks go in panels of PN <= 8 so that the PN
     // accumulator tiles stay in registers.
     template <class N, int L>
     __device__ __forceinline__ void layer_mma(const float* __restrict__ sw, int lane, int t, const uint32_t (&ah)[N::in16(L) / 16][4],
@@ -132,31 +130,41 @@ namespace
 #pragma unroll
         for (int np = 0; np < NT; np += PN)
         {
-            float acc[3][PN][4]; // [0] A_lo*B_hi, [1] A_hi*B_lo (scaled by 2^11), [2] bias + A_hi*B_hi
+            // bias + A_hi*B_hi + A_lo*B_hi + A_hi*B_lo: the three products of the split operands (A_lo*B_lo is below fp32
+            // resolution) go into ONE fp32 accumulator tile per output block when the panel is wide: per k block the products
+            // are issued pass by pass, so the HMMAs of one accumulator are PN instructions apart (a dependent HMMA waits 21
+            // cycles for its predecessor).  Narrow panels keep one tile per product and add them at the end.
+            constexpr int NA = PN >= 4 ? 1 : 3;
+            float acc[NA][PN][4];
 #pragma unroll
             for (int j = 0; j < PN; ++j)
             {
                 const float4 b = B[(np + j) * 4]; // one LDS.128 straight into the accumulator tile
-                acc[2][j][0] = b.x, acc[2][j][1] = b.y, acc[2][j][2] = b.z, acc[2][j][3] = b.w;
+                acc[0][j][0] = b.x, acc[0][j][1] = b.y, acc[0][j][2] = b.z, acc[0][j][3] = b.w;
 #pragma unroll
-                for (int i = 0; i < 4; ++i) acc[0][j][i] = 0.f, acc[1][j][i] = 0.f;
+                for (int q = 1; q < NA; ++q)
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) acc[q][j][i] = 0.f;
             }
 #pragma unroll
             for (int kt = 0; kt < KT; ++kt)
+            {
+                uint4 w[PN]; // {b0_hi, b1_hi, b0_lo, b1_lo}
 #pragma unroll
-                for (int j = 0; j < PN; ++j)
-                {
-                    const uint4 w = W[((np + j) * KT + kt) * 32]; // {b0_hi, b1_hi, b0_lo, b1_lo}
-                    mma_f16(acc[0][j], al[kt], w.x, w.y);
-                    mma_f16(acc[1][j], ah[kt], w.z, w.w);
-                    mma_f16(acc[2][j], ah[kt], w.x, w.y);
-                }
+                for (int j = 0; j < PN; ++j) w[j] = W[((np + j) * KT + kt) * 32];
+#pragma unroll
+                for (int j = 0; j < PN; ++j) mma_f16(acc[1 % NA][j], al[kt], w[j].x, w[j].y);
+#pragma unroll
+                for (int j = 0; j < PN; ++j) mma_f16(acc[2 % NA][j], ah[kt], w[j].z, w[j].w);
+#pragma unroll
+                for (int j = 0; j < PN; ++j) mma_f16(acc[0][j], ah[kt], w[j].x, w[j].y);
+            }
 #pragma unroll
             for (int j = 0; j < PN; ++j)
             {
                 float v[4];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) v[i] = ll_tanh_approx(fmaf(acc[1][j][i], LO_UNSCALE, acc[2][j][i] + acc[0][j][i]));
+                for (int i = 0; i < 4; ++i) v[i] = ll_tanh_approx(NA == 1 ? acc[0][j][i] : acc[0][j][i] + (acc[1 % NA][j][i] + acc[2 % NA][j][i]));
                 if constexpr (LAST)
                 {
 #pragma unroll
@@ -207,7 +215,7 @@ namespace
                 if (o < OUT)
                 {
                     const __half hi = __float2half_rn(fminf(fmaxf(e[j], -65504.f), 65504.f));
-                    const __half lo = __float2half_rn(fminf(fmaxf((e[j] - __half2float(hi)) * LO_SCALE, -65504.f), 65504.f));
+                    const __half lo = __float2half_rn(fminf(fmaxf(e[j] - __half2float(hi), -65504.f), 65504.f)); // unscaled: exact to 2^-25 absolute
                     const int word  = ((((o >> 3) * KT + (k >> 4)) * 32 + (o & 7) * 4 + ((k & 7) >> 1)) << 2) + ((k >> 3) & 1);
                     dst[word * 2 + (k & 1)]       = hi;
                     dst[(word + 2) * 2 + (k & 1)] = lo;

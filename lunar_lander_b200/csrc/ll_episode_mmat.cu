@@ -26,6 +26,9 @@
 
 #include "ll_env.cuh"
 
+#ifndef LL_MMAT_ONE_ACC
+#define LL_MMAT_ONE_ACC 2
+#endif
 #ifndef LL_MMAT_PANEL
 #define LL_MMAT_PANEL 8 /* accumulator tiles (x3 split products) alive at once */
 #endif
@@ -48,12 +51,10 @@ namespace
         static __host__ __device__ constexpr int k16(int l) { return (sz(l) + 15) & ~15; }
         static __host__ __device__ constexpr int m16(int l) { return (sz(l + 1) + 15) & ~15; }
         // shared-memory layout in 32-bit words: per layer the A fragments [m16/16][k16/16][hi, lo][32 lanes][4 words] (one word per
-        // weight), then the bias [m16/16][8 (g)][2] = {b[16mt + g], b[16mt + g + 8]}.  Two layers keep half fragments: the first has
-        // at most 8 inputs (k 8..15 of its only k tile is padding: words a2, a3 are zero and not stored), the last at most 8 outputs
-        // (rows 8..15 of its only output tile: a1, a3).  For 16_64_32 that is 14.3 instead of 15.9 KB per member: 15 warps per SM.
-        static __host__ __device__ constexpr bool half_k(int l) { return NL > 1 && l == 0 && sz(0) <= 8; }
-        static __host__ __device__ constexpr bool half_m(int l) { return NL > 1 && l == NL - 1 && sz(NL) <= 8; }
-        static __host__ __device__ constexpr int w_words(int l) { return (half_k(l) || half_m(l)) ? m16(l) * k16(l) / 2 : m16(l) * k16(l); }
+        // weight), then the bias [m16/16][8 (g)][2] = {b[16mt + g], b[16mt + g + 8]}.  The first layer has at most 8 inputs: its
+        // fragments are those of mma.m16n8k8 (2 words per lane; k 8..15 would be padding).
+        static __host__ __device__ constexpr bool half_k(int l) { return l == 0 && sz(0) <= 8; }
+        static __host__ __device__ constexpr int w_words(int l) { return half_k(l) ? m16(l) * k16(l) / 2 : m16(l) * k16(l); }
         static __host__ __device__ constexpr int w_off(int l)
         {
             int o = 0;
@@ -79,8 +80,7 @@ namespace
         int w_off[LL_MAX_LAYERS], b_off[LL_MAX_LAYERS], out_pad[LL_MAX_LAYERS]; // the HBM row layout (ll_topo)
     };
 
-    constexpr float T_LO_SCALE = 2048.f, T_LO_UNSCALE = 1.f / 2048.f;
-
+    
     __device__ __forceinline__ void mma_w(float (&c)[4], const uint4& w, uint32_t b0, uint32_t b1)
     {
         asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
@@ -105,20 +105,21 @@ namespace
         lo = *reinterpret_cast<const uint32_t*>(&pl);
     }
 
-    // A fragment (hi: hl = 0, scaled lo: hl = 1) of tile (mt, kt) of layer L from a staged row
-    template <class N, int L> __device__ __forceinline__ uint4 load_w(const float* __restrict__ row, int lane, int tile, int hl)
+    // m16n8k8 for the first layer (inputs 0..7 are the whole k extent): the fragment is a uint2
+    __device__ __forceinline__ void mma_w(float (&c)[4], const uint2& w, uint32_t b0, uint32_t)
     {
-        if constexpr (N::half_k(L))
-        {
-            const uint2 v = reinterpret_cast<const uint2*>(row + N::w_off(L))[(tile * 2 + hl) * 32 + lane];
-            return make_uint4(v.x, v.y, 0u, 0u);
-        }
-        else if constexpr (N::half_m(L))
-        {
-            const uint2 v = reinterpret_cast<const uint2*>(row + N::w_off(L))[(tile * 2 + hl) * 32 + lane];
-            return make_uint4(v.x, 0u, v.y, 0u);
-        }
-        else return reinterpret_cast<const uint4*>(row + N::w_off(L))[(tile * 2 + hl) * 32 + lane];
+        asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
+                     : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                     : "r"(w.x), "r"(w.y), "r"(b0));
+    }
+    template <bool HALF> struct wfrag { using type = uint4; };
+    template <> struct wfrag<true> { using type = uint2; };
+
+    // A fragment (hi: hl = 0, lo: hl = 1) of tile mt * KT + kt of layer L from a member's staged row
+    template <class N, int L> __device__ __forceinline__ typename wfrag<N::half_k(L)>::type load_w(const float* __restrict__ row, int lane, int tile, int hl)
+    {
+        using F = typename wfrag<N::half_k(L)>::type;
+        return reinterpret_cast<const F*>(row + N::w_off(L))[(tile * 2 + hl) * 32 + lane];
     }
 
     // One layer for the warp's NT slot tiles.  xh/xl[j][kt][2]: B fragments (hi / lo) of slot tile j, k tile kt.  Output: the next
@@ -138,7 +139,12 @@ namespace
 #pragma unroll
         for (int mp = 0; mp < MT; mp += PM)
         {
-            float acc[3][PM][NT][4]; // [0] W_hi*X_lo, [1] W_lo'*X_hi (scaled by 2^11), [2] bias + W_hi*X_hi
+            // bias + W_hi*X_hi + W_hi*X_lo + W_lo*X_hi in ONE fp32 accumulator tile per (output tile, slot tile) when the layer has
+            // at least LL_MMAT_ONE_ACC output tiles (per k tile the products go pass by pass, so the HMMAs of one accumulator are
+            // PM * NT instructions apart); single-tile layers keep one tile per product and add them at the end.  The rule looks
+            // at the layer only, so every kernel variant rounds alike.
+            constexpr int NA = MT >= LL_MMAT_ONE_ACC ? 1 : 3;
+            float acc[NA][PM][NT][4];
 #pragma unroll
             for (int i = 0; i < PM; ++i)
             {
@@ -146,26 +152,32 @@ namespace
 #pragma unroll
                 for (int j = 0; j < NT; ++j)
                 {
-                    acc[2][i][j][0] = b.x, acc[2][i][j][1] = b.x, acc[2][i][j][2] = b.y, acc[2][i][j][3] = b.y;
+                    acc[0][i][j][0] = b.x, acc[0][i][j][1] = b.x, acc[0][i][j][2] = b.y, acc[0][i][j][3] = b.y;
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) acc[0][i][j][e] = 0.f, acc[1][i][j][e] = 0.f;
+                    for (int q = 1; q < NA; ++q)
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) acc[q][i][j][e] = 0.f;
                 }
             }
 #pragma unroll
             for (int kt = 0; kt < KT; ++kt)
+            {
+                typename wfrag<N::half_k(L)>::type wh[PM], wl[PM];
+#pragma unroll
+                for (int i = 0; i < PM; ++i) wh[i] = load_w<N, L>(sw, lane, (mp + i) * KT + kt, 0), wl[i] = load_w<N, L>(sw, lane, (mp + i) * KT + kt, 1);
 #pragma unroll
                 for (int i = 0; i < PM; ++i)
-                {
-                    const uint4 wh = load_w<N, L>(sw, lane, (mp + i) * KT + kt, 0);
-                    const uint4 wl = load_w<N, L>(sw, lane, (mp + i) * KT + kt, 1);
 #pragma unroll
-                    for (int j = 0; j < NT; ++j)
-                    {
-                        mma_w(acc[0][i][j], wh, xl[j][kt][0], xl[j][kt][1]);
-                        mma_w(acc[1][i][j], wl, xh[j][kt][0], xh[j][kt][1]);
-                        mma_w(acc[2][i][j], wh, xh[j][kt][0], xh[j][kt][1]);
-                    }
-                }
+                    for (int j = 0; j < NT; ++j) mma_w(acc[1 % NA][i][j], wh[i], xl[j][kt][0], xl[j][kt][1]);
+#pragma unroll
+                for (int i = 0; i < PM; ++i)
+#pragma unroll
+                    for (int j = 0; j < NT; ++j) mma_w(acc[2 % NA][i][j], wl[i], xh[j][kt][0], xh[j][kt][1]);
+#pragma unroll
+                for (int i = 0; i < PM; ++i)
+#pragma unroll
+                    for (int j = 0; j < NT; ++j) mma_w(acc[0][i][j], wh[i], xh[j][kt][0], xh[j][kt][1]);
+            }
 #pragma unroll
             for (int i = 0; i < PM; ++i)
 #pragma unroll
@@ -173,7 +185,8 @@ namespace
                     {
                         float v[4];
 #pragma unroll
-                        for (int e = 0; e < 4; ++e) v[e] = ll_tanh_approx(fmaf(acc[1][i][j][e], T_LO_UNSCALE, acc[2][i][j][e] + acc[0][i][j][e]));
+                        for (int e = 0; e < 4; ++e)
+                            v[e] = ll_tanh_approx(NA == 1 ? acc[0][i][j][e] : acc[0][i][j][e] + (acc[1 % NA][i][j][e] + acc[2 % NA][i][j][e]));
                         if constexpr (LAST)
                         {
                             if (mp + i == 0) z[j][0] = v[0], z[j][1] = v[1];
@@ -223,12 +236,12 @@ namespace
                 if (o < OUT)
                 {
                     const __half hi = __float2half_rn(fminf(fmaxf(e[q], -65504.f), 65504.f));
-                    const __half lo = __float2half_rn(fminf(fmaxf((e[q] - __half2float(hi)) * T_LO_SCALE, -65504.f), 65504.f));
+                    const __half lo = __float2half_rn(fminf(fmaxf(e[q] - __half2float(hi), -65504.f), 65504.f)); // unscaled: exact to 2^-25 absolute
                     const int r = o & 15, c = k & 15;
                     const int tile = (o >> 4) * KT + (k >> 4);
                     const int ln   = (r & 7) * 4 + ((c & 7) >> 1);
-                    constexpr int FW = (N::half_k(L) || N::half_m(L)) ? 2 : 4; // words per lane in a fragment
-                    const int word = N::half_k(L) ? (r >> 3) : (N::half_m(L) ? (c >> 3) : (r >> 3) + 2 * (c >> 3));
+                    constexpr int FW = N::half_k(L) ? 2 : 4; // words per lane in a fragment
+                    const int word = N::half_k(L) ? (r >> 3) : (r >> 3) + 2 * (c >> 3);
                     const int base = ((tile * 2) * 32 + ln) * FW + word; // hi fragment; the lo fragment is 32 * FW words further
                     dst[base * 2 + (c & 1)]             = hi;
                     dst[(base + 32 * FW) * 2 + (c & 1)] = lo;
