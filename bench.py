@@ -224,7 +224,9 @@ def ncu_traffic(workload, members):
 # (ll_episode_mmat.cu, slots on the N side: ceil(in/16) * ceil(out/16) tiles for an 8-slot tile)
 def hmma_flop_per_step(sizes, transposed=False):
     if transposed:
-        tiles = sum(((sizes[i] + 15) // 16) * ((sizes[i + 1] + 15) // 16) for i in range(len(sizes) - 1))
+        # the first layer (<= 8 inputs) uses m16n8k8: half a tile of work
+        tiles = sum(((sizes[i] + 15) // 16) * ((sizes[i + 1] + 15) // 16) * (0.5 if i == 0 and sizes[0] <= 8 else 1.0)
+                    for i in range(len(sizes) - 1))
         return tiles * 3 * 2 * 16 * 8 * 16 / 8.0
     tiles = sum(((sizes[i] + 15) // 16) * ((sizes[i + 1] + 7) // 8) for i in range(len(sizes) - 1))
     return tiles * 3 * 2 * 16 * 8 * 16 / 16.0
