@@ -109,7 +109,10 @@ namespace
         T bv[TILE];
         vec_loader<T, TILE>::load(b, bv);
 #pragma unroll
-        for (int i = 0; i < TILE; ++i) aout[i * 32] = O::act(O::add(acc[i], bv[i]), act);
+        for (int i = 0; i < TILE; ++i) acc[i] = O::add(acc[i], bv[i]);
+        O::template act_n<TILE>(acc, act);
+#pragma unroll
+        for (int i = 0; i < TILE; ++i) aout[i * 32] = acc[i];
     }
 
     // Whole forward pass; returns the index of the first maximum of the output layer.

@@ -125,6 +125,65 @@ LL_HD double ll_tanh(double x)
     return ll_u2d(ll_d2u(z) | sign);
 }
 
+// ll_tanh of N values at once, stage by stage and without branches: a scalar ll_tanh is a chain of ~45 dependent operations and
+// a division, N chains side by side fill the pipeline (the exact episode kernel calls this with the 8 or 16 neurons of a tile).
+// Every element goes through exactly the operations of ll_tanh in the same order, so the results are bit-identical; elements in
+// the special ranges (NaN, |x| >= 22, |x| < 2^-28) run the main path on a harmless stand-in and are replaced at the end.
+template <int N> LL_HD void ll_tanh_n(const double (&x)[N], double (&y)[N])
+{
+    const double invln2 = 1.4426950408889634, ln2_hi = 6.93147180369123816490e-01, ln2_lo = 1.90821492927058770002e-10;
+    const double c[13] = {1.1470745597729725e-11, 1.6059043836821613e-10, 2.08767569878681e-09,  2.505210838544172e-08,  2.755731922398589e-07,
+                          2.7557319223985893e-06, 2.48015873015873e-05,   0.0001984126984126984, 0.001388888888888889,   0.008333333333333333,
+                          0.041666666666666664,   0.16666666666666666,    0.5};
+    uint64_t sign[N], uax[N];
+    double r[N], q[N], kd[N];
+    int k[N];
+LL_UNROLL
+    for (int i = 0; i < N; ++i)
+    {
+        const uint64_t ux = ll_d2u(x[i]);
+        sign[i]           = ux & 0x8000000000000000ull;
+        uax[i]            = ux & 0x7fffffffffffffffull;
+        const bool main_r = uax[i] < 0x4036000000000000ull && uax[i] >= 0x3e30000000000000ull;
+        const double ax   = main_r ? ll_u2d(uax[i]) : 1.0;
+        r[i]              = LL_ADD(ax, ax); // y = 2|x|
+    }
+LL_UNROLL
+    for (int i = 0; i < N; ++i) q[i] = LL_MUL(r[i], invln2);
+LL_UNROLL
+    for (int i = 0; i < N; ++i) k[i] = (int)(q[i] < 0.0 ? LL_SUB(q[i], 0.5) : LL_ADD(q[i], 0.5)), kd[i] = (double)k[i];
+LL_UNROLL
+    for (int i = 0; i < N; ++i) r[i] = LL_SUB(LL_SUB(r[i], LL_MUL(kd[i], ln2_hi)), LL_MUL(kd[i], ln2_lo));
+LL_UNROLL
+    for (int i = 0; i < N; ++i) q[i] = c[0];
+LL_UNROLL
+    for (int j = 1; j < 13; ++j)
+LL_UNROLL
+        for (int i = 0; i < N; ++i) q[i] = LL_ADD(LL_MUL(q[i], r[i]), c[j]);
+LL_UNROLL
+    for (int i = 0; i < N; ++i) q[i] = LL_ADD(r[i], LL_MUL(LL_MUL(r[i], r[i]), q[i])); // p = expm1(r)
+LL_UNROLL
+    for (int i = 0; i < N; ++i)
+    {
+        const double s = ll_pow2i(k[i]);
+        const double e = LL_ADD(LL_MUL(s, q[i]), LL_SUB(s, 1.0));
+        q[i]           = k[i] != 0 ? e : q[i]; // em1
+    }
+LL_UNROLL
+    for (int i = 0; i < N; ++i) r[i] = LL_ADD(q[i], 2.0);
+LL_UNROLL
+    for (int i = 0; i < N; ++i) q[i] = LL_DIV(q[i], r[i]);
+LL_UNROLL
+    for (int i = 0; i < N; ++i)
+    {
+        double z = ll_u2d(ll_d2u(q[i]) | sign[i]);
+        if (uax[i] < 0x3e30000000000000ull) z = x[i];
+        if (uax[i] >= 0x4036000000000000ull) z = ll_u2d(sign[i] | 0x3ff0000000000000ull);
+        if (uax[i] > 0x7ff0000000000000ull) z = LL_ADD(x[i], x[i]);
+        y[i] = z;
+    }
+}
+
 // exp(x) for |x| < 700, used by ll_sigmoid.
 LL_HD double ll_exp(double x)
 {

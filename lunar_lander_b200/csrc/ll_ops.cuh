@@ -27,6 +27,28 @@ template <> struct ll_ops<float, LL_MODE_EXACT>
         const double zd = (double)z;
         return (float)(id == LL_ACT_TANH ? ll_tanh(zd) : ll_sigmoid(zd));
     }
+    template <int N> static __device__ __forceinline__ void act_n(float (&v)[N], int id)
+    {
+        if (id == LL_ACT_TANH)
+        {
+            constexpr int B = N > 8 ? 8 : N; // 8 double chains at a time (registers)
+#pragma unroll
+            for (int o = 0; o < N; o += B)
+            {
+                double x[B], y[B];
+#pragma unroll
+                for (int i = 0; i < B; ++i) x[i] = (double)v[o + i];
+                ll_tanh_n<B>(x, y);
+#pragma unroll
+                for (int i = 0; i < B; ++i) v[o + i] = (float)y[i];
+            }
+        }
+        else
+        {
+#pragma unroll
+            for (int i = 0; i < N; ++i) v[i] = act(v[i], id);
+        }
+    }
 };
 
 template <> struct ll_ops<double, LL_MODE_EXACT>
@@ -39,6 +61,21 @@ template <> struct ll_ops<double, LL_MODE_EXACT>
     static __device__ __forceinline__ double sqrt(double a) { return __dsqrt_rn(a); }
     static __device__ __forceinline__ double madd(double acc, double w, double a) { return __dadd_rn(acc, __dmul_rn(w, a)); }
     static __device__ __forceinline__ double act(double z, int id) { return id == LL_ACT_TANH ? ll_tanh(z) : ll_sigmoid(z); }
+    template <int N> static __device__ __forceinline__ void act_n(double (&v)[N], int id)
+    { // the N activations of a tile of neurons: tanh chains side by side (ll_tanh_n), bit-identical to act() on each
+        if (id == LL_ACT_TANH)
+        {
+            double y[N];
+            ll_tanh_n<N>(v, y);
+#pragma unroll
+            for (int i = 0; i < N; ++i) v[i] = y[i];
+        }
+        else
+        {
+#pragma unroll
+            for (int i = 0; i < N; ++i) v[i] = act(v[i], id);
+        }
+    }
 };
 
 __device__ __forceinline__ float ll_tanh_approx(float x)
@@ -61,6 +98,11 @@ template <> struct ll_ops<float, LL_MODE_FAST>
     {
         // sigmoid(z) = 0.5 * tanh(z / 2) + 0.5
         return id == LL_ACT_TANH ? ll_tanh_approx(z) : fmaf(0.5f, ll_tanh_approx(0.5f * z), 0.5f);
+    }
+    template <int N> static __device__ __forceinline__ void act_n(float (&v)[N], int id)
+    {
+#pragma unroll
+        for (int i = 0; i < N; ++i) v[i] = act(v[i], id);
     }
 };
 
