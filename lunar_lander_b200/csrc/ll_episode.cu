@@ -424,9 +424,7 @@ namespace
         a.trace = h.trace, a.trace_cap = h.trace_cap, a.trace_result = h.trace_result;
         const int L = h.n_layouts;
         // Geometry of a warp tile: Q lanes per episode slot, G slots per member, nslots members.  Q = 1 (a lane walks all neurons of
-        // its episode) unless lanes would idle (below).  Forcing Q > 1 on a SMALL population to get more warps does not pay
-        // (configs[0], 100 x 50: 148 / 168 / 197 / 372 ms per generation for Q = 1 / 2 / 4 / 8): a generation lasts as long as its longest
-        // lane's chain of dependent fp64 operations, and fewer slots per warp mean more sequential rounds.  LL_EXACT_Q forces a value.
+        // its episode) unless lanes would idle or the population is too small to fill the GPU (both below).  LL_EXACT_Q forces a value.
         auto geometry = [&](int q, int* g_out, int* nslots_out) {
             const int E = 32 / q;
             int G       = 1;
@@ -449,6 +447,21 @@ namespace
             int widest = 4;
             for (int l = 0; l < tp.n_layers; ++l) widest = std::max(widest, tp.out_pad[l]);
             while (Q * 2 * g1 * n1 <= 32 && Q * 2 <= widest / 4 && Q < 8) Q <<= 1;
+            // small population (the reference's own scale): a generation lasts as long as one lane's chain of steps, each a few
+            // thousand fp64 instructions of ONE warp - deal the neurons of a slot to up to 4 lanes (and its layouts to more warps,
+            // below) while the GPU has warps to spare.  configs[0], 100 x 50: 46.5 / 31.9 / 25.4 / 26.6 ms for Q = 1 / 2 / 4 / 8.
+            if (Q == 1 && h.ep_steps && h.ep_fit)
+                for (int q = 4; q > 1; q >>= 1)
+                {
+                    int g = 0, n = 0;
+                    const unsigned long long tiles = geometry(q, &g, &n);
+                    const unsigned long long ch    = L > 32 / q ? (unsigned long long)((L + 32 / q - 1) / (32 / q)) : 1ull;
+                    if (q <= widest / 4 && tiles * ch <= (unsigned long long)ctx->sm_count * 8ull)
+                    {
+                        Q = q;
+                        break;
+                    }
+                }
             const char* force = getenv("LL_EXACT_Q");
             if (force && *force)
             {
