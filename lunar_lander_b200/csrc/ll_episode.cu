@@ -58,6 +58,7 @@ namespace
         int slot_stride;          // elements between member rows in shared memory
         int width_a, width_b;     // rows of the two activation buffers: a0 holds the inputs and the outputs of the odd layers, a1 the even ones
         int off_w, off_act, off_fit, off_meta, warp_bytes; // byte offsets inside a warp's shared-memory slice
+        int act_pitch;                                     // row pitch of the activation buffers, elements
     };
 
     template <typename T, int N> struct vec_loader;
@@ -88,10 +89,11 @@ namespace
 
     // TILE consecutive output neurons of one layer for this lane's episode.
     //   w   : &Wt[0][o0] of the lane's member (shared memory), row pitch out_pad
-    //   ain : this lane's activation column of the previous layer, element k at ain[k * 32]
+    //   ain : this lane's activation column of the previous layer, element k at ain[k * P] (P: row pitch of the activation
+    //         buffers in elements, 32 = one column per lane)
     template <typename T, int MODE, int TILE>
     __device__ __forceinline__ void layer_tile(const T* __restrict__ w, const T* __restrict__ b, const T* __restrict__ ain,
-                                               T* __restrict__ aout, int in, int out_pad, int act)
+                                               T* __restrict__ aout, int in, int out_pad, int act, int P)
     {
         using O = ll_ops<T, MODE>;
         T acc[TILE];
@@ -100,7 +102,7 @@ namespace
 #pragma unroll 2
         for (int k = 0; k < in; ++k)
         {
-            const T a = ain[k * 32];
+            const T a = ain[k * P];
             T wv[TILE];
             vec_loader<T, TILE>::load(w + k * out_pad, wv);
 #pragma unroll
@@ -112,7 +114,7 @@ namespace
         for (int i = 0; i < TILE; ++i) acc[i] = O::add(acc[i], bv[i]);
         O::template act_n<TILE>(acc, act);
 #pragma unroll
-        for (int i = 0; i < TILE; ++i) aout[i * 32] = acc[i];
+        for (int i = 0; i < TILE; ++i) aout[i * P] = acc[i];
     }
 
     // Whole forward pass; returns the index of the first maximum of the output layer.
@@ -120,7 +122,7 @@ namespace
     // own arithmetic (sequential-k multiply-add, bias last, activation) is untouched, so the result is bit-identical to Q == 1.
     // Every lane of the warp must call this together when Q > 1 (warp barriers between layers).
     template <typename T, int MODE>
-    __device__ __forceinline__ int forward(const ll_topo& tp, const T* __restrict__ wrow, T* a0, T* a1, int sub = 0, int Q = 1)
+    __device__ __forceinline__ int forward(const ll_topo& tp, const T* __restrict__ wrow, T* a0, T* a1, int sub = 0, int Q = 1, int P = 32)
     {
         constexpr int BIG = sizeof(T) == 4 ? 16 : 8;
         T* ain  = a0;
@@ -132,21 +134,21 @@ namespace
             const T* b = wrow + tp.b_off[l];
             if (Q > 1)
             {
-                for (int o = sub * 4; o < op; o += Q * 4) layer_tile<T, MODE, 4>(w + o, b + o, ain, aout + o * 32, in, op, tp.activation);
+                for (int o = sub * 4; o < op; o += Q * 4) layer_tile<T, MODE, 4>(w + o, b + o, ain, aout + o * P, in, op, tp.activation, P);
                 __syncwarp();
             }
             else
             {
                 int o = 0;
-                for (; o + BIG <= op; o += BIG) layer_tile<T, MODE, BIG>(w + o, b + o, ain, aout + o * 32, in, op, tp.activation);
+                for (; o + BIG <= op; o += BIG) layer_tile<T, MODE, BIG>(w + o, b + o, ain, aout + o * P, in, op, tp.activation, P);
                 if (BIG == 16 && o + 8 <= op)
                 {
-                    layer_tile<T, MODE, 8>(w + o, b + o, ain, aout + o * 32, in, op, tp.activation);
+                    layer_tile<T, MODE, 8>(w + o, b + o, ain, aout + o * P, in, op, tp.activation, P);
                     o += 8;
                 }
                 if (o + 4 <= op)
                 {
-                    layer_tile<T, MODE, 4>(w + o, b + o, ain, aout + o * 32, in, op, tp.activation);
+                    layer_tile<T, MODE, 4>(w + o, b + o, ain, aout + o * P, in, op, tp.activation, P);
                     o += 4;
                 }
             }
@@ -159,7 +161,7 @@ namespace
         T vbest         = ain[0];
         for (int j = 1; j < n_out; ++j)
         {
-            const T v = ain[j * 32];
+            const T v = ain[j * P];
             if (v > vbest) vbest = v, best = j;
         }
         if (Q > 1) __syncwarp(); // the outputs are read before any lane overwrites the buffers with the next step's state
@@ -172,7 +174,7 @@ namespace
 
     // get_state(): src/game_logic.cpp:275-293
     template <typename T, int MODE>
-    __device__ __forceinline__ void write_state(const ll_env<T>& e, T x, T y, T vx, T vy, T fuel, T cx, T* col)
+    __device__ __forceinline__ void write_state(const ll_env<T>& e, T x, T y, T vx, T vy, T fuel, T cx, T* col, int P = 32)
     {
         using O = ll_ops<T, MODE>;
         T s0, s1, s2, s3, s4;
@@ -187,14 +189,16 @@ namespace
             s0 = O::div(vx, e.max_vx), s1 = O::div(vy, e.max_vy), s2 = O::div(dx, e.width);
             s3 = O::div(dy, e.height), s4 = O::div(fuel, e.max_fuel);
         }
-        col[0 * 32] = clampT(s0, T(-2), T(2));
-        col[1 * 32] = clampT(s1, T(-2), T(2));
-        col[2 * 32] = clampT(s2, T(-5), T(5));
-        col[3 * 32] = clampT(s3, T(-5), T(5));
-        col[4 * 32] = s4;
+        col[0 * P] = clampT(s0, T(-2), T(2));
+        col[1 * P] = clampT(s1, T(-2), T(2));
+        col[2 * P] = clampT(s2, T(-5), T(5));
+        col[3 * P] = clampT(s3, T(-5), T(5));
+        col[4 * P] = s4;
     }
 
-    template <typename T, int MODE>
+    // RP: the activation buffers have a run-time row pitch (Q > 1 and wide layers, see the launcher); otherwise the pitch is the
+    // constant 32 and a slot's column is its first lane, which keeps the address arithmetic of the inner loops in immediates.
+    template <typename T, int MODE, bool RP>
     __global__ void __launch_bounds__(128) ll_episode_kernel(const __grid_constant__ ll_topo tp, const __grid_constant__ ll_env<T> env,
                                                              const __grid_constant__ ep_dev_args a)
     {
@@ -206,8 +210,10 @@ namespace
         int* next_layout  = reinterpret_cast<int*>(ws + 16);
         T* wsm            = reinterpret_cast<T*>(ws + a.off_w);
         const int Q = a.Q, sub = lane % Q, elane = lane / Q; // Q lanes share one episode slot (and its activation column)
-        T* act0           = reinterpret_cast<T*>(ws + a.off_act) + (lane - sub);
-        T* act1           = act0 + a.width_a * 32;
+        // activation buffers: row pitch P elements, the slot's column = elane (P = 32 and column = lane when Q == 1)
+        const int P       = RP ? a.act_pitch : 32;
+        T* act0           = reinterpret_cast<T*>(ws + a.off_act) + (RP ? elane : lane - sub);
+        T* act1           = act0 + a.width_a * P;
         double* res_fit   = reinterpret_cast<double*>(ws + a.off_fit);
         int* res_meta     = reinterpret_cast<int*>(ws + a.off_meta);
 
@@ -267,8 +273,8 @@ namespace
 
             while (__any_sync(0xffffffffu, active))
             {
-                write_state<T, MODE>(env, x, y, vx, vy, fuel, cx, act0);
-                const int action = forward<T, MODE>(tp, wrow, act0, act1, sub, Q);
+                write_state<T, MODE>(env, x, y, vx, vy, fuel, cx, act0, P);
+                const int action = forward<T, MODE>(tp, wrow, act0, act1, sub, Q, P);
                 if (active)
                 {
                     // apply_action: src/game_logic.cpp:156-183
@@ -305,8 +311,8 @@ namespace
                     {
                         ll_step_rec r;
                         r.action = (double)action;
-                        write_state<T, MODE>(env, x, y, vx, vy, fuel, cx, act0);
-                        for (int i = 0; i < 5; ++i) r.state[i] = (double)act0[i * 32];
+                        write_state<T, MODE>(env, x, y, vx, vy, fuel, cx, act0, P);
+                        for (int i = 0; i < 5; ++i) r.state[i] = (double)act0[i * P];
                         r.x = (double)x, r.y = (double)y, r.vx = (double)vx, r.vy = (double)vy, r.fuel = (double)fuel;
                         a.trace[steps] = r;
                     }
@@ -521,7 +527,22 @@ namespace
             w      = std::max(w, tp.out_pad[l]);
         }
         a.width_a = std::max(a.width_a, 8);
-        a.off_fit = up(a.off_act + (a.width_a + a.width_b) * 32 * (int)sizeof(T));
+        // Row pitch of the activation buffers.  Q == 1: one column per lane, pitch 32.  Q > 1: E = 32 / Q columns; the Q lanes of a
+        // slot store rows 4 apart (their tiles of 4 neurons), so the pitch is the smallest P >= E with 4 P = E modulo one sweep of
+        // the banks (128 B) - the Q row segments of a store then tile the banks instead of piling onto the same ones (pitch 32 and
+        // columns Q apart: 8-way conflicts on every activation store of 16_64_32 fp64, ncu).
+        a.act_pitch = 32;
+        int widest_out = 4;
+        for (int l = 0; l < tp.n_layers; ++l) widest_out = std::max(widest_out, tp.out_pad[l]);
+        const bool rp = Q > 1 && widest_out >= 32; // narrow networks store little: the constant pitch is faster there (16_16: 6 %)
+        if (rp)
+        {
+            const int E = 32 / Q, W = 128 / (int)sizeof(T);
+            int P = E;
+            while ((4 * P) % W != E % W) ++P;
+            a.act_pitch = P;
+        }
+        a.off_fit = up(a.off_act + (a.width_a + a.width_b) * a.act_pitch * (int)sizeof(T));
         const int R   = std::max(32, a.nslots * L); // per-layout results of every member of the tile (indexed slot * L + layout)
         a.off_meta    = a.off_fit + R * 8;
         a.warp_bytes  = up(a.off_meta + R * 4);
@@ -533,7 +554,7 @@ namespace
         int wpb = 4;
         while (wpb > 1 && wpb * a.warp_bytes > max_smem / 2) wpb >>= 1; // prefer >= 2 blocks per SM
         const size_t smem = (size_t)wpb * a.warp_bytes;
-        auto kern         = ll_episode_kernel<T, MODE>;
+        auto kern         = rp ? ll_episode_kernel<T, MODE, true> : ll_episode_kernel<T, MODE, false>;
         LL_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int per_sm = 0;
         LL_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, wpb * 32, smem));
