@@ -9,14 +9,14 @@
 //     D[out x slots] = W[out x in] * X[in x slots],   M = 16 output neurons, N = 8 slots, K = 16 inputs per HMMA
 //   * an N tile is 8 slots: 8 layouts fill it completely, and a warp that owns 16 slots (two N tiles) skips the HMMAs, the
 //     epilogue and the environment of a tile whose 8 episodes have all ended (a warp-uniform switch to a one-tile pass);
-//   * the weights are the A operand: split once per member into fp16 hi / scaled lo and stored as ready-made A fragments,
+//   * the weights are the A operand: split once per member into fp16 hi / lo and stored as ready-made A fragments,
 //     one LDS.128 each per (output tile, k tile, lane), shared by the warp's N tiles; the bias is a float2 per (tile, g);
 //   * activations stay in registers: the D fragment of layer l (rows = outputs g / g+8, columns = slots 2t, 2t+1), after
 //     tanh and the hi/lo split, becomes the B fragment of k tile = output tile of layer l+1 (k = 2t, 2t+1 / 2t+8, 2t+9, column =
 //     slot g) through one movmatrix.m8n8.trans per 8x8 block — the only extra cost of the transposed form;
 //   * the lander of slot g lives, replicated, in the four lanes of quad g: each lane builds its own pair of layer-0 inputs
 //     without a shuffle; the 4 outputs of a slot sit in lanes g = 0..3 of one column and are gathered with three shuffles.
-// fp32 accuracy from fp16 operands exactly as in ll_episode_mma.cu: D = W_hi X_hi + W_hi X_lo + 2^-11 W_lo' X_hi.
+// fp32 accuracy from fp16 operands exactly as in ll_episode_mma.cu: D = bias + W_hi X_hi + W_hi X_lo + W_lo X_hi, one accumulator tile.
 #include <cuda_fp16.h>
 
 #include <algorithm>
@@ -27,10 +27,10 @@
 #include "ll_env.cuh"
 
 #ifndef LL_MMAT_ONE_ACC
-#define LL_MMAT_ONE_ACC 2
+#define LL_MMAT_ONE_ACC 2 /* layers with at least this many output tiles keep ONE accumulator tile per output tile */
 #endif
 #ifndef LL_MMAT_PANEL
-#define LL_MMAT_PANEL 8 /* accumulator tiles (x3 split products) alive at once */
+#define LL_MMAT_PANEL 8 /* output tiles of a layer processed together (their accumulator tiles and weight fragments live in registers) */
 #endif
 
 #ifndef LL_MMAT_MEMBERS_DEFAULT
