@@ -388,6 +388,17 @@ extern "C"
     }
 
     double orc_tanh(double x) { return ll_tanh(x); }
+    // ll_tanh_n (the exact kernel's tile-wide tanh, csrc/ll_math.h) on n values, 8 at a time: must equal orc_tanh bit for bit
+    void orc_tanh_n(const double* x, double* y, uint64_t n)
+    {
+        for (uint64_t o = 0; o < n; o += 8)
+        {
+            double xi[8], yi[8];
+            for (int i = 0; i < 8; ++i) xi[i] = o + i < n ? x[o + i] : 0.0;
+            ll_tanh_n<8>(xi, yi);
+            for (int i = 0; i < 8 && o + i < n; ++i) y[o + i] = yi[i];
+        }
+    }
     double orc_sigmoid(double x) { return ll_sigmoid(x); }
     void orc_normal_pair(uint32_t seed, uint32_t gen, uint32_t member, uint32_t pair, double* n0, double* n1) { ll_normal_pair(seed, gen, member, pair, n0, n1); }
     uint32_t orc_parent_pick(uint32_t seed, uint32_t gen, uint32_t member, uint32_t top) { return ll_parent_pick(seed, gen, member, top); }

@@ -38,6 +38,8 @@ def port() -> C.CDLL:
         _port = C.CDLL(PORT_PATH)
         _port.orc_tanh.restype = C.c_double
         _port.orc_tanh.argtypes = [C.c_double]
+        _port.orc_tanh_n.restype = None
+        _port.orc_tanh_n.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
         _port.orc_sigmoid.restype = C.c_double
         _port.orc_sigmoid.argtypes = [C.c_double]
         _port.orc_parent_pick.restype = C.c_uint32
