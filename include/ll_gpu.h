@@ -288,6 +288,11 @@ int ll_step_counter(ll_ctx* ctx, double* total_steps, uint64_t* evaluations, int
  * per SM, 194: one warp per sub-partition, 195: one warp per sub-partition with a single dependent accumulator chain,
  * 196/198: rotating operands at one/two warps per sub-partition, 197: m16n8k16 f16 with rotating operands), 16 -> mma.sync.m16n8k16 bf16 (warp-level tensor-core rate).  Result in TFLOP/s (2 flop per FMA). */
 int ll_microbench_fma(int32_t device, int32_t precision, double seconds, double* tflops, double* sm_mhz_est);
+/* tcgen05 (5th-generation tensor core) known-answer tests and issue-rate / hop-latency microbenchmarks on `device`:
+ * args[16] = {test, m_instr, n, k, a_mn_major, b_mn_major, swap_lbo_sbo, iters, n_acc, busy_warps, busy_iters, mufu_every,
+ * group_threads, all_sms, a_from_tmem, lane_off}; d_out (test 0 only): [128][n] floats, the raw TMEM dump; result[16] per test, see
+ * csrc/ll_tc05_probe.cu.  Fails with LL_ENODEVICE on anything but sm_100. */
+int ll_tc05_probe(int32_t device, const int32_t* args, float* d_out, double* result);
 /* HBM copy bandwidth (read+write bytes / time), GB/s */
 int ll_microbench_copy(int32_t device, uint64_t bytes, int32_t iters, double* gbps);
 
