@@ -283,10 +283,10 @@ int ll_kernel_times_get(ll_ctx* ctx, ll_kernel_times* out, int reset);
 /* lander steps (= feedforward calls, the reference's Sum all_member_steps, src/nn_engine_trainer.cpp:519,530) executed by
  * all evaluations since the last reset, accumulated on the device so that timed loops need no per-generation read */
 int ll_step_counter(ll_ctx* ctx, double* total_steps, uint64_t* evaluations, int reset);
-/* FMA-pipe roofline denominator measured on this device: dependent-free FMA chains for ~`seconds`.
- * precision 32 -> FFMA, 322 -> packed FFMA2 (fma.rn.f32x2), 64 -> DFMA; 19 -> mma.sync.m16n8k8 tf32 (191: at 16 warps
- * per SM, 194: one warp per sub-partition, 195: one warp per sub-partition with a single dependent accumulator chain,
- * 196/198: rotating operands at one/two warps per sub-partition, 197: m16n8k16 f16 with rotating operands), 16 -> mma.sync.m16n8k16 bf16 (warp-level tensor-core rate).  Result in TFLOP/s (2 flop per FMA). */
+/* FMA-pipe roofline denominator measured on this device: dependency-free FMA chains for ~`seconds`, MEAN over the loop.
+ * precision 32 -> FFMA, 322 -> packed FFMA2 (fma.rn.f32x2), 64 -> DFMA, 197 -> mma.sync.m16n8k16 f16 with rotating operands at one
+ * warp per SM sub-partition (the legacy tensor pipe of the mma / mmat episode kernels).  Result in TFLOP/s (2 flop per FMA);
+ * sm_mhz_est = SM cycles per nanosecond of one thread over the same loop (clock64 / %globaltimer). */
 int ll_microbench_fma(int32_t device, int32_t precision, double seconds, double* tflops, double* sm_mhz_est);
 /* tcgen05 (5th-generation tensor core) known-answer tests and issue-rate / hop-latency microbenchmarks on `device`:
  * args[16] = {test, m_instr, n, k, a_mn_major, b_mn_major, swap_lbo_sbo, iters, n_acc, busy_warps, busy_iters, mufu_every,

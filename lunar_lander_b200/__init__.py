@@ -3,7 +3,7 @@
 The package holds only what that path needs: ``csrc/`` (CUDA kernels + the C ABI of include/ll_gpu.h, built into
 ``libll_gpu.so`` next to this file) and the host-side mirrors of the reference's interfaces for it: ``config.Config``,
 ``engine.Engine`` (the network + population behind the C ABI), ``trainer.NNEngineTrainer`` (the sharded multi-GPU trainer),
-``lunar_lander_cpp`` / ``cpp_nn_py`` / ``nn_play`` (the nn_play side), and in ``host/`` the C++ mirror (``main_train_d/_f``).
+``nn_play`` (the headless nn_play loop over the pybind11 modules ``lunar_lander_cpp`` / ``cpp_nn_py`` built into ``pymodules/``), and in ``host/`` the C++ mirror (``main_train_d/_f``).
 Importing it requires the built library; there is no CPU fallback.
 """
 from . import _abi  # noqa: F401  (raises ImportError when libll_gpu.so has not been built)

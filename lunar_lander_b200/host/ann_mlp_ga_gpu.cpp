@@ -44,7 +44,9 @@ namespace nn
         sizes_ = sizes, pop_ = pop, top_ = top, act_ = act, seed_ = seed;
         std::vector<uint64_t> s(sizes.begin(), sizes.end());
         const bool is_float    = std::is_same<T, float>::value;
-        const std::string mode = Config::getStringOr("GpuCfg.mode", is_float ? "fast" : "exact");
+        const std::string mode = mode_override_ == LL_MODE_EXACT  ? "exact"
+                                 : mode_override_ == LL_MODE_FAST ? "fast"
+                                                                  : Config::getStringOr("GpuCfg.mode", is_float ? "fast" : "exact");
         if (mode != "exact" && mode != "fast") throw std::runtime_error("GpuCfg.mode must be exact or fast, got " + mode);
         if (mode == "fast" && !is_float) throw std::runtime_error("GpuCfg.mode = fast needs the float build (main_train_f)");
         ll_env_cfg env = Config::envCfg();

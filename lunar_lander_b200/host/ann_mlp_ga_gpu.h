@@ -65,6 +65,8 @@ namespace nn
         double TotalLanderSteps(bool reset);
         std::string KernelName() const;
         ll_ctx* Context() const { return ctx_; }
+        // LL_MODE_EXACT / LL_MODE_FAST for the next open (constructor with sizes or Deserialize); default: GpuCfg.mode
+        void SetMode(int mode) { mode_override_ = mode; }
 
       private:
         void open(const std::vector<size_t>& sizes, uint64_t seed, size_t pop, size_t top, size_t act);
@@ -80,6 +82,7 @@ namespace nn
         int strategy_     = LL_STRATEGY_MIXED_WITH_RANDOM_INJECTION;
         double ratio_     = 0.0;
         bool strategy_set_ = false;
+        int mode_override_ = -1;
     };
 } // namespace nn
 

@@ -9,26 +9,37 @@ What is kept, line for line in behaviour (main.py:127-238):
     frames — starts it with a forced UP (action 1); afterwards the network's action is used as is;
   * per updated frame ``penalty += calculate_step_penalty(action)``, at game over ``penalty += calculate_terminal_penalty(steps)``.
 
-Everything numeric runs on the GPU: the lander through ``lunar_lander_cpp`` (ll_sim_*), the policy through ``cpp_nn_py``
-(ll_feedforward_index).
+Everything numeric runs on the GPU: the lander through the pybind11 module ``lunar_lander_cpp`` (ll_sim_*), the policy through
+the pybind11 module ``cpp_nn_py`` (ll_feedforward_index).  Both are imported by their top-level names from ``pymodules/`` — the
+directory a user of the reference puts on ``sys.path`` in place of ``externals/ma-libs/build/Release`` (main.py:19-21,
+mod_nn_play.py:15-17).
 """
 from __future__ import annotations
 
 import os
+import sys
 from dataclasses import dataclass, field
 from typing import Callable, List, Optional
 
 import numpy as np
 
-from . import cpp_nn_py, lunar_lander_cpp
 from .config import Config
+
+PYMODULES = os.path.join(os.path.dirname(os.path.abspath(__file__)), "pymodules")
+if PYMODULES not in sys.path:
+    sys.path.append(PYMODULES)
+try:
+    import cpp_nn_py  # noqa: E402
+    import lunar_lander_cpp  # noqa: E402
+except ModuleNotFoundError as e:  # no fallback: the native modules are the only implementation
+    raise ImportError(f"{e}; build them with `make -C lunar_lander_b200/host` (or __graft_entry__.build())") from e
 
 
 class NeuralNetwork:
     """mod_nn_play.NeuralNetwork (mod_nn_play.py:25-59)."""
 
     def __init__(self, cfg: Config, weights: Optional[str] = None):
-        self._net = cpp_nn_py.ANN_MLP_GA_double(cfg)
+        self._net = cpp_nn_py.ANN_MLP_GA_double()
         name = cfg.getString("NNConfig.name")
         self._net.SetName(name)
         path = weights or os.path.join(cfg.getString("NNConfig.save_path_nn"), f"{name}_last.txt")

@@ -155,6 +155,8 @@ namespace
     // a_{l+1} = act(W_l a_l + b_l) on every layer, W_l [out][in] row-major (canonical member layout), ascending-k
     // accumulation from 0 with separate multiply and add, bias added last, activation = ll_math.h evaluated in double,
     // action = first maximum.  PARITY UNPINNED (see header).
+    int g_libm_activation = 0; // orc_set_activation_impl
+
     template <typename T> struct Net
     {
         std::vector<uint64_t> sizes;
@@ -172,6 +174,9 @@ namespace
         }
         T activate(T z) const
         {
+            // SURVEY.md H2 cross-check: libm's tanh / exp evaluated in T (what a C++ template library most plausibly calls), independent
+            // of the product's csrc/ll_math.h — only used to measure how far the deterministic ll_tanh moves the action sequences
+            if (g_libm_activation) return act == LL_ACT_TANH ? std::tanh(z) : T(1) / (T(1) + std::exp(-z));
             const double zd = static_cast<double>(z);
             return static_cast<T>(act == LL_ACT_TANH ? ll_tanh(zd) : ll_sigmoid(zd));
         }
@@ -320,6 +325,9 @@ namespace
 
 extern "C"
 {
+    // 0: ll_tanh / ll_sigmoid of csrc/ll_math.h in double (default, what the exact kernels use); 1: libm std::tanh / std::exp in T
+    void orc_set_activation_impl(int libm) { g_libm_activation = libm ? 1 : 0; }
+
     unsigned orc_hardware_threads() { return std::max(1u, std::thread::hardware_concurrency()); }
 
     int orc_evaluate_f64(const ll_env_cfg* cfg, const uint64_t* sizes, int n_sizes, int act, uint64_t pop, const double* params,

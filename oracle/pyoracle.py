@@ -109,6 +109,11 @@ def create_population(sizes, seed, pop, top, gen, strategy, ratio, elitism, has_
     return p
 
 
+def set_activation_impl(libm: bool) -> None:
+    """False (default): the deterministic ll_tanh of csrc/ll_math.h; True: libm's std::tanh evaluated in T (SURVEY.md H2 cross-check)."""
+    port().orc_set_activation_impl(1 if libm else 0)
+
+
 def topk(fitness, k):
     f = np.ascontiguousarray(fitness, dtype=np.float64)
     out = np.zeros(k, dtype=np.uint64)

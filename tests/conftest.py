@@ -20,7 +20,9 @@ def built():
     lib = os.path.join(ROOT, "lunar_lander_b200", "libll_gpu.so")
     port = os.path.join(ROOT, "oracle", "_build", "libll_oracle.so")
     host = os.path.join(ROOT, "lunar_lander_b200", "host", "bin", "main_train_d")
-    if not (os.path.exists(lib) and os.path.exists(port) and os.path.exists(host)):
+    pymods = os.path.join(ROOT, "lunar_lander_b200", "pymodules")
+    have_py = os.path.isdir(pymods) and sum(f.endswith(".so") for f in os.listdir(pymods)) >= 2
+    if not (os.path.exists(lib) and os.path.exists(port) and os.path.exists(host) and have_py):
         g.build()
     return True
 

@@ -590,3 +590,50 @@ def test_config3_properties_and_sample(ll, po):
     assert np.array_equal(fit[pick], want["fitness"]) and np.array_equal(steps[pick], want["steps"])
     assert np.array_equal(eng.select(None), po.topk(fit, 10))
     eng.close()
+
+
+@pytest.mark.parametrize("topo,pop,n_layouts", [("16_64_32", 65536, 8), ("32_128_32", 131072, 50)])
+def test_fast_mode_at_benchmark_size(ll, po, topo, pop, n_layouts):
+    """The configurations bench.py times, at the size it times them, in the mode it times them (LL_MODE_FAST, default kernel):
+    configs[2] (16_64_32, 65 536 x 8) and the configs[3] shard (32_128_32, 131 072 x 50).  The population is what the bench flies: the
+    sample-run elites, bred once by config.txt's GA (elitism, 35 % random injection).  Whole population: size-independent invariants
+    (steps == sum of episode steps, 9 <= steps <= max_steps, flag exclusivity, device top-k == host (fitness, index) order).
+    A strided sample of 256 members against the fp32 oracle with the fast-mode tolerances of test_fast_mode_outcomes (success rate
+    within 2 points, total steps within 2 %, mean fitness within 3 % of mean |fitness|), and the same sample in EXACT mode bit-equal
+    to the oracle."""
+    sizes = util.TOPOLOGIES[topo]
+    eng, cfg = _engine(ll, sizes, pop, 32, mode=1, top=10)
+    eng.set_population_strategy(2, 0.35)
+    e, _ = util.elites(topo)
+    eng.set_members(0, e)
+    eng.mark_elites()
+    eng.create_population(True)
+    spad, lpad, d = util.layouts(50)
+    spad, lpad, d = spad[:n_layouts], lpad[:n_layouts], d[:n_layouts]
+    fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
+    kernel = eng.info.kernel.decode()
+    ep_steps, ep_flags, ep_fit = eng.read_episodes()
+    assert ep_steps.min() >= 9 and ep_steps.max() <= 5000
+    assert np.array_equal(steps, ep_steps.sum(axis=1).astype(np.float64))
+    assert st.sum_steps == steps.sum() and st.members == pop
+    assert np.all(((ep_flags & 4) == 0) | ((ep_flags & 2) == 0))          # success and crashed are exclusive
+    assert np.all((ep_flags & 1) == ((ep_flags >> 1) & 1) | ((ep_flags >> 2) & 1))  # landed == crashed or success
+    assert np.all((ep_steps == 5000) | ((ep_flags & 1) == 1))            # an episode that did not touch down ran to max_steps
+    assert np.all(np.isfinite(fit)) and np.all(lr >= 0)
+    assert np.array_equal(eng.select(None), po.topk(fit, 10))            # device radix top-k == host sort by (fitness, index)
+    pick = np.arange(0, pop, pop // 256)[:256]
+    sub = np.stack([eng.get_members(int(i), 1)[0] for i in pick])
+    eng.close()
+    want = po.evaluate(cfg.env_cfg(), sizes, 1, sub, spad, lpad, d, 5000, 32, threads=po.port().orc_hardware_threads())
+    rate_gpu, rate_cpu = (ep_flags[pick] & 4).astype(bool).mean(), (want["ep_flags"] & 4).astype(bool).mean()
+    assert abs(rate_gpu - rate_cpu) <= 0.02, (kernel, rate_gpu, rate_cpu)
+    assert abs(steps[pick].sum() - want["steps"].sum()) <= 0.02 * want["steps"].sum(), (kernel, steps[pick].sum(), want["steps"].sum())
+    scale = np.abs(want["fitness"]).mean()
+    assert abs(fit[pick].mean() - want["fitness"].mean()) <= 0.03 * scale, (kernel, fit[pick].mean(), want["fitness"].mean())
+    assert np.mean(ep_steps[pick] == want["ep_steps"]) >= 0.9, kernel
+    # the same members in exact mode: bit-equal
+    ex, _ = _engine(ll, sizes, len(pick), 32, mode=0, top=10)
+    ex.set_members(0, sub)
+    f2, l2, s2, _ = ex.evaluate(spad, lpad, d, 5000)
+    assert np.array_equal(f2, want["fitness"]) and np.array_equal(s2, want["steps"]) and np.array_equal(l2, want["lr"])
+    ex.close()

@@ -19,8 +19,8 @@ SAMPLE = os.path.join(util.GOLDEN, "sample_lunar_lander_5_8_16_8_4_s_0500.txt")
 @pytest.fixture(scope="module")
 def mods(built):
     import pyoracle as po
-    from lunar_lander_b200 import cpp_nn_py, lunar_lander_cpp, nn_play
-    return po, lunar_lander_cpp, cpp_nn_py, nn_play
+    from lunar_lander_b200 import nn_play
+    return po, nn_play.lunar_lander_cpp, nn_play.cpp_nn_py, nn_play
 
 
 def oracle_trace(po, sizes, params, spad, lpad, direction, max_steps, precision, fixed_action=-1):
@@ -100,8 +100,10 @@ def test_binding_errors_and_members(mods, tmp_path):
         logic.get_state(np.zeros((5, 1)))  # src/lunar_lander_cpp.cpp:50
     with pytest.raises(RuntimeError, match="1-dimensional"):
         logic.update(0, np.zeros((1, 5)))  # :63
-    with pytest.raises(TypeError):
-        logic.update(0, np.zeros(5, dtype=np.float32))  # pybind rejects the wrong dtype for array_t<double>... by conversion
+    wrong = np.full(5, 7.0, dtype=np.float32)  # py::array_t<double> converts a float32 array into a temporary: the call succeeds
+    logic.update(0, wrong)                     # and the caller's buffer stays untouched, exactly like the reference binding
+    assert np.all(wrong == 7.0)
+    logic.reset()
     with pytest.raises(AssertionError):
         logic.calculate_terminal_penalty_lr_bonus(10, 2)
     logic.reset(100, 500)
@@ -173,3 +175,88 @@ def test_trained_file_plays(mods, tmp_path):
     r = play.nn_play(cfg, os.path.join(d, "data", "lunar_lander_last.txt"), seed=7, log=lambda s: None)
     assert r.steps > 0 and r.frames >= r.steps and (r.game_over or r.frames == 5000 + 180)
     assert ROOT
+
+
+REF_SEQUENCE = r'''
+# the literal call sequence of the reference: main.py:19-28 (imports by top-level name), mod_nn_play.py:26-59 (NeuralNetwork),
+# main.py:127-142 (logic + pads), :192-238 (nn_play branch of the loop) — pygame removed, time = frame counter at 60 fps
+import sys, os, json
+import numpy as np
+import lunar_lander_cpp
+import cpp_nn_py
+from lunar_lander_cpp import GameLogicCppDouble as GameLogicCpp
+from lunar_lander_cpp import generate_random_pad_positions
+
+class NeuralNetwork():
+    def __init__(self):
+        self._net = cpp_nn_py.ANN_MLP_GA_double()
+        self._net.SetName("lunar_lander")
+        full_path = os.path.join("./data/", "lunar_lander_last.txt")
+        self._net.Deserialize(full_path)
+        self._nGen = self._net.GetEpochs()
+        self._nnsize = self._net.GetNetworkSize()
+    def get_action(self, current_state):
+        inputs = np.array(current_state, dtype=np.float64)
+        return self._net.feedforwardIndex(inputs, 0)
+
+logic = GameLogicCpp(False, 'config.txt')
+spad_x1, lpad_x1 = generate_random_pad_positions(960, 80, 200, seed=int(sys.argv[1]), force_left_to_right=False, force_right_to_left=False)
+logic.reset(spad_x1, lpad_x1)
+NN = NeuralNetwork()
+game_over = has_started = False
+penalty, current_game_steps, frame = 0.0, 0, 0
+state_buffer = np.zeros(5, dtype=np.float64)
+actions = []
+while frame < 5180 and not game_over:
+    action = 0
+    logic.get_state(state_buffer)
+    nn_action = NN.get_action(state_buffer)
+    if not has_started:
+        if frame * 1000.0 / 60.0 > 2000:
+            action = 1; has_started = True
+        elif nn_action != 0:
+            action = 1; has_started = True
+    else:
+        action = nn_action
+    if has_started and not game_over:
+        done = logic.update(action, state_buffer)
+        penalty += logic.calculate_step_penalty(action)
+        current_game_steps += 1
+        actions.append(int(action))
+        if done:
+            game_over = True
+    if game_over:
+        penalty += logic.calculate_terminal_penalty(current_game_steps)
+    frame += 1
+print(json.dumps({"gen": NN._nGen, "size": list(NN._nnsize), "pads": [spad_x1, lpad_x1], "steps": current_game_steps, "frames": frame,
+                  "landed": bool(logic.landed_successfully), "crashed": bool(logic.crashed), "penalty": penalty, "x": logic.x, "y": logic.y,
+                  "fuel": logic.fuel, "actions": actions, "modules": [lunar_lander_cpp.__file__, cpp_nn_py.__file__]}))
+'''
+
+
+def test_reference_imports_and_call_sequence_in_a_fresh_interpreter(mods, tmp_path):
+    """INTEGRATION.md §3 literally: a fresh interpreter whose only extra sys.path entry is lunar_lander_b200/pymodules imports
+    `lunar_lander_cpp` and `cpp_nn_py` BY THOSE TOP-LEVEL NAMES (main.py:19-28, mod_nn_play.py:15-20), loads the
+    data/lunar_lander_last.txt written by main_train_f and flies main.py's nn_play loop; the result equals the in-package
+    headless loop on the same file and seed."""
+    import json
+    import subprocess
+    import sys
+    _, _, _, play = mods
+    from test_gpu_host import BIN, write_config
+    d = str(tmp_path)
+    write_config(d, **{"NNConfig.hlayers": "8,16,8", "NNConfig.epochs": 3, "NNConfig.population_size": 64, "NNTrainingCfg.layout_nb": 4})
+    p = subprocess.run([os.path.join(BIN, "main_train_f")], cwd=d, capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr
+    assert os.path.exists(os.path.join(d, "data", "lunar_lander_last.txt"))
+    env = {k: v for k, v in os.environ.items() if k != "PYTHONPATH"}
+    env["PYTHONPATH"] = play.PYMODULES
+    q = subprocess.run([sys.executable, "-c", REF_SEQUENCE, "7"], cwd=d, capture_output=True, text=True, timeout=300, env=env)
+    assert q.returncode == 0, q.stderr + q.stdout
+    got = json.loads(q.stdout.strip().splitlines()[-1])
+    assert all(os.path.dirname(m) == play.PYMODULES for m in got["modules"])  # the native extension modules, nothing else
+    assert got["gen"] == 3 and got["size"] == [5, 8, 16, 8, 4]
+    r = play.nn_play(os.path.join(d, "config.txt"), os.path.join(d, "data", "lunar_lander_last.txt"), seed=7, log=lambda s: None, fps=60.0)
+    assert (got["pads"], got["steps"], got["frames"]) == ([r.spad_x1, r.lpad_x1], r.steps, r.frames)
+    assert got["actions"] == r.actions and got["penalty"] == r.penalty
+    assert (got["landed"], got["crashed"], got["x"], got["y"], got["fuel"]) == (r.landed_successfully, r.crashed, r.x, r.y, r.fuel)

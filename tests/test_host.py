@@ -68,6 +68,66 @@ def test_cpp_host_trainer_refuses_without_gpu(built, tmp_path):
     assert "libll_gpu.so" in out and "oracle" not in out
 
 
+def test_python_drop_in_modules_import_by_their_top_level_names(built, tmp_path):
+    """with lunar_lander_b200/pymodules on sys.path (and nothing else of this repo) a fresh interpreter imports
+    `lunar_lander_cpp` and `cpp_nn_py` the way main.py:24-28 and mod_nn_play.py:20 do; names and defaults are the reference's
+    (src/lunar_lander_cpp.cpp:21-106, mod_nn_play.py:28-56); without a GPU construction fails loudly, nothing computes on the CPU."""
+    import json
+    import torch
+    code = r'''
+import json, sys
+import numpy as np
+import lunar_lander_cpp, cpp_nn_py
+from lunar_lander_cpp import GameLogicCppDouble as GameLogicCpp
+from lunar_lander_cpp import generate_random_pad_positions
+out = {"files": [lunar_lander_cpp.__file__, cpp_nn_py.__file__]}
+out["pads"] = list(generate_random_pad_positions(960.0, 80, 200, seed=5247))
+out["pads_kw"] = list(generate_random_pad_positions(screen_width=960.0, spad_width=80, lpad_width=200, seed=None, force_left_to_right=True, force_right_to_left=False))
+for cls in (lunar_lander_cpp.GameLogicCppDouble, lunar_lander_cpp.GameLogicCppFloat):
+    for name in ("x", "y", "vx", "vy", "fuel", "landed", "crashed", "landed_successfully", "landing_pad_center_x", "landing_pad_y", "no_print",
+                 "last_action", "reset", "is_done", "get_state", "update", "calculate_step_penalty", "calculate_terminal_penalty",
+                 "calculate_terminal_penalty_lr_bonus"):
+        assert hasattr(cls, name), name
+for cls in (cpp_nn_py.ANN_MLP_GA_double, cpp_nn_py.ANN_MLP_GA_float):
+    for name in ("SetName", "Deserialize", "Serialize", "GetEpochs", "GetNetworkSize", "GetPopSize", "GetTopPerformersSize", "feedforwardIndex"):
+        assert hasattr(cls, name), name
+try:
+    GameLogicCpp(False, "no_such_config.txt")
+    out["missing_cfg"] = "no error"
+except RuntimeError as e:
+    out["missing_cfg"] = str(e)
+try:
+    GameLogicCpp(True, sys.argv[1])
+    out["ctor"] = "ok"
+except RuntimeError as e:
+    out["ctor"] = str(e)
+net = cpp_nn_py.ANN_MLP_GA_double()
+net.SetName("lunar_lander")
+out["epochs_empty"] = net.GetEpochs()
+try:
+    net.feedforwardIndex(np.zeros(5), 0)
+    out["ff_empty"] = "no error"
+except RuntimeError as e:
+    out["ff_empty"] = str(e)
+print(json.dumps(out))
+'''
+    pymods = os.path.join(util.ROOT, "lunar_lander_b200", "pymodules")
+    env = {k: v for k, v in os.environ.items() if k != "PYTHONPATH"}
+    env["PYTHONPATH"] = pymods
+    p = subprocess.run([sys.executable, "-c", code, util.CFG_PATH], cwd=tmp_path, capture_output=True, text=True, env=env, timeout=300)
+    assert p.returncode == 0, p.stderr
+    out = json.loads(p.stdout.strip().splitlines()[-1])
+    assert all(os.path.dirname(f) == pymods and f.endswith(".so") for f in out["files"])
+    assert out["pads"] == [402, 131]  # libstdc++ mt19937(5247) + uniform_int_distribution, SURVEY.md App. D
+    assert out["pads_kw"][0] + 40 < out["pads_kw"][1] + 100
+    assert out["missing_cfg"] == "FATAL: Could not load configuration from no_such_config.txt. Exiting."  # src/game_logic.cpp:44
+    assert out["epochs_empty"] == 0 and "no shape" in out["ff_empty"]
+    if torch.cuda.is_available():
+        assert out["ctor"] == "ok"
+    else:
+        assert "no CUDA device" in out["ctor"]
+
+
 def test_product_does_not_link_the_oracle(ll):
     from lunar_lander_b200 import _abi
     out = subprocess.run(["ldd", _abi.LIB_PATH], capture_output=True, text=True).stdout
