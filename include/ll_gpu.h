@@ -178,7 +178,8 @@ int ll_get_epochs(const ll_ctx* ctx, uint64_t* out);
 int ll_set_epochs(ll_ctx* ctx, uint64_t epochs);
 
 /* replaces  std::sort of indices by fitness + UpdateWeightsAndBiases(sorted_indices)
- *           src/nn_engine_trainer.cpp:376-379, 404        (single process, world == 1)
+ *           src/nn_engine_trainer.cpp:376-379, 404        (world == 1, or any world once ll_comm_init has been called:
+ *           then every rank makes the same call and sorted_idx must be the same on all of them)
  * sorted_idx: `n_sorted` (>= top) GLOBAL indices in ascending-fitness order as the reference computes them on
  * the host, or NULL: then the elites are chosen on the device from the last ll_evaluate, ordered by
  * (fitness, index).  elite_idx_out (may be NULL) receives the `top` chosen indices. */
@@ -195,6 +196,20 @@ int ll_local_topk(ll_ctx* ctx, ll_cand* out, uint64_t* n_out);
 int ll_gather_elites(ll_ctx* ctx, const uint64_t* elite_idx, uint64_t n, void* device_buf);
 int ll_set_elites(ll_ctx* ctx, const void* device_buf, uint64_t n);
 uint64_t ll_elite_buffer_bytes(const ll_ctx* ctx);
+
+/* ---- the exchange between GPUs, owned by the context --------------------------------------------------
+ * replaces  nothing in the reference (it is single-process); it is what lets std::sort + UpdateWeightsAndBiases
+ *           (src/nn_engine_trainer.cpp:376-379, 404) and the thread-pool fan-out (:460-538) span several GPUs.
+ * One context per GPU (one host thread or one process each), created with rank/world.  Rank 0 obtains an id, the host hands its
+ * LL_COMM_ID_BYTES bytes to every rank (threads: memcpy; processes: MPI / a torch store / a file), every rank calls ll_comm_init
+ * (collective: ncclCommInitRank).  From then on ll_step_generation and ll_select work on shards: K2 local top-k -> NCCL all-gather
+ * of top x 16 B -> one-block merge by (fitness, index) -> K3 row gather -> NCCL all-reduce of the [top][params_padded] parent
+ * matrix, enqueued on the context's stream with no host synchronisation in between; ll_gen_stats then describe the WHOLE population
+ * on every rank.  NCCL is dlopen'ed (libnccl.so.2); without it these calls fail with LL_ENODEVICE. */
+#define LL_COMM_ID_BYTES 128
+int ll_comm_get_unique_id(void* id_out);
+int ll_comm_init(ll_ctx* ctx, const void* unique_id);
+int ll_comm_destroy(ll_ctx* ctx);
 
 /* ---- evaluation: the hot path ------------------------------------------------------------------------------
  * replaces  NNEngineTrainer<T>::train_generation(layouts, layout_directions, population_size, fitness_scores,
@@ -214,7 +229,7 @@ int ll_read_results(ll_ctx* ctx, double* fitness, double* last_gen_lr, double* s
  *   fitness = terminal penalty + accumulated step penalties of that layout        (:514-517) */
 int ll_read_episodes(ll_ctx* ctx, int32_t* meta, double* fitness);
 
-/* one whole generation without a host round trip in the middle (world == 1):
+/* one whole generation without a host round trip in the middle (world == 1, or shards with a communicator):
  * evaluate -> device top-k -> elite gather -> children -> epochs += 1   (src/nn_engine_trainer.cpp:373-407) */
 int ll_step_generation(ll_ctx* ctx, int32_t max_steps, int elitism, ll_gen_stats* stats);
 

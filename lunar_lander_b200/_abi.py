@@ -100,6 +100,9 @@ SIGNATURES = {
     "ll_gather_elites": (C.c_int, [_ctx, _u64p, C.c_uint64, C.c_void_p]),
     "ll_set_elites": (C.c_int, [_ctx, C.c_void_p, C.c_uint64]),
     "ll_elite_buffer_bytes": (C.c_uint64, [_ctx]),
+    "ll_comm_get_unique_id": (C.c_int, [C.c_void_p]),
+    "ll_comm_init": (C.c_int, [_ctx, C.c_void_p]),
+    "ll_comm_destroy": (C.c_int, [_ctx]),
     "ll_evaluate": (C.c_int, [_ctx, _i32p, _i32p, _u64p, C.c_int32, C.c_int32, _f64p, _f64p, _f64p, C.POINTER(GenStats)]),
     "ll_set_layouts": (C.c_int, [_ctx, _i32p, _i32p, _u64p, C.c_int32]),
     "ll_evaluate_device": (C.c_int, [_ctx, C.c_int32]),

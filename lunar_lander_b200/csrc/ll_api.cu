@@ -53,28 +53,21 @@ struct ll_prof_holder
 {
     prof_state st;
 };
-static std::vector<std::pair<ll_ctx*, ll_prof_holder*>> g_prof; // tiny registry: contexts are few and long-lived
 
 namespace
 {
     prof_state* prof_of(ll_ctx* ctx)
     {
-        for (auto& p : g_prof)
-            if (p.first == ctx) return &p.second->st;
-        g_prof.emplace_back(ctx, new ll_prof_holder());
-        return &g_prof.back().second->st;
+        if (!ctx->prof) ctx->prof = new ll_prof_holder();
+        return &ctx->prof->st;
     }
     void prof_drop(ll_ctx* ctx)
     {
-        for (size_t i = 0; i < g_prof.size(); ++i)
-            if (g_prof[i].first == ctx)
-            {
-                for (auto& t : g_prof[i].second->st.pending) cudaEventDestroy(t.a), cudaEventDestroy(t.b);
-                for (auto& t : g_prof[i].second->st.pool) cudaEventDestroy(t.a), cudaEventDestroy(t.b);
-                delete g_prof[i].second;
-                g_prof.erase(g_prof.begin() + (long)i);
-                return;
-            }
+        if (!ctx->prof) return;
+        for (auto& t : ctx->prof->st.pending) cudaEventDestroy(t.a), cudaEventDestroy(t.b);
+        for (auto& t : ctx->prof->st.pool) cudaEventDestroy(t.a), cudaEventDestroy(t.b);
+        delete ctx->prof;
+        ctx->prof = nullptr;
     }
 
     scope::scope(ll_ctx* c, int cl, uint64_t launches) : ctx(c), cls(cl)
@@ -134,15 +127,7 @@ namespace
     }
 } // namespace
 
-// dev2canon lives with the context but ll_ctx is shared with non-API translation units; keep it in a side table
-static std::vector<std::pair<const ll_ctx*, std::vector<int>>> g_d2c;
-static const std::vector<int>& d2c_of(const ll_ctx* ctx)
-{
-    for (auto& p : g_d2c)
-        if (p.first == ctx) return p.second;
-    static const std::vector<int> empty;
-    return empty;
-}
+static const std::vector<int>& d2c_of(const ll_ctx* ctx) { return ctx->d2c; }
 
 void ll_set_error(ll_ctx* ctx, const std::string& msg)
 {
@@ -175,12 +160,7 @@ extern "C" void ll_destroy(ll_ctx* ctx)
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     prof_drop(ctx);
-    for (size_t i = 0; i < g_d2c.size(); ++i)
-        if (g_d2c[i].first == ctx)
-        {
-            g_d2c.erase(g_d2c.begin() + (long)i);
-            break;
-        }
+    ll_comm_release(ctx);
     void* ptrs[] = {ctx->d_params, ctx->d_elites,   ctx->d_dev2canon, ctx->d_layouts, ctx->d_fitness, ctx->d_lr,        ctx->d_steps,
                     ctx->d_ep_steps, ctx->d_ep_fit, ctx->d_queue,     ctx->d_stats,   ctx->d_partials, ctx->d_sel,      ctx->d_keys,
                     ctx->d_cand,   ctx->d_elite_idx, ctx->d_trace,    ctx->d_scratch, ctx->d_sim, ctx->d_part};
@@ -285,7 +265,7 @@ extern "C" int ll_create(ll_ctx** out, const ll_env_cfg* env, const ll_net_cfg* 
     LL_CUDA_B(cudaMemsetAsync(ctx->d_scratch, 0, 1024, ctx->stream));
     LL_CUDA_B(cudaStreamSynchronize(ctx->stream));
 #undef LL_CUDA_B
-    g_d2c.emplace_back(ctx, std::move(d2c));
+    ctx->d2c = std::move(d2c);
     *out = ctx;
     return LL_OK;
 }
@@ -390,7 +370,8 @@ static int device_topk(ll_ctx* ctx, unsigned int k)
 extern "C" int ll_select(ll_ctx* ctx, const uint64_t* sorted_idx, uint64_t n_sorted, uint64_t* elite_idx_out)
 {
     LL_CHECK_CTX(ctx);
-    if (ctx->world != 1) return ll_fail(ctx, LL_EINVAL, "ll_select is single-shard; use ll_local_topk/ll_gather_elites/ll_set_elites");
+    if (ctx->world != 1 && !ctx->comm)
+        return ll_fail(ctx, LL_EINVAL, "ll_select on a shard needs a communicator (ll_comm_init), or use ll_local_topk/ll_gather_elites/ll_set_elites");
     const unsigned int k = (unsigned int)ctx->top;
     if (sorted_idx)
     {
@@ -402,8 +383,14 @@ extern "C" int ll_select(ll_ctx* ctx, const uint64_t* sorted_idx, uint64_t n_sor
         LL_CUDA(ctx, cudaMemcpyAsync(ctx->d_elite_idx, ctx->h_pin, sizeof(uint64_t) * k, cudaMemcpyHostToDevice, ctx->stream));
         LL_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     }
-    else { LL_TRY(device_topk(ctx, k)); }
-    LL_TRY(install_elites_from_idx(ctx, k));
+    else if (ctx->world == 1) { LL_TRY(device_topk(ctx, k)); }
+    if (ctx->world == 1) { LL_TRY(install_elites_from_idx(ctx, k)); }
+    else
+    { // every rank makes the same call: all-gather of the local top-k + merge (no indices given), row gather + all-reduce
+        if (!sorted_idx && !ctx->have_results) return ll_fail(ctx, LL_EINVAL, "selection needs the results of ll_evaluate");
+        scope s(ctx, CLS_SELECT, sorted_idx ? 1 : 1 + 12 + 1 + 1 + 4);
+        LL_TRY(ll_comm_select(ctx, sorted_idx != nullptr));
+    }
     if (elite_idx_out)
     {
         LL_TRY(ensure_pinned(ctx, sizeof(uint64_t) * k));
@@ -528,6 +515,7 @@ extern "C" int ll_evaluate_device(ll_ctx* ctx, int32_t max_steps)
         LL_TRY(ll_launch_stats(ctx));
     }
     ctx->have_results = true;
+    ctx->stats_global = false;
     return LL_OK;
 }
 
@@ -551,7 +539,7 @@ extern "C" int ll_read_results(ll_ctx* ctx, double* fitness, double* last_gen_lr
         ll_stats_dev sd;
         std::memcpy(&sd, h + 3 * n, sizeof(sd));
         stats->best_fitness = sd.best_fitness, stats->best_index = sd.best_index, stats->sum_fitness = sd.sum_fitness;
-        stats->sum_steps = sd.sum_steps, stats->best_lr = sd.best_lr, stats->members = ctx->pop_local;
+        stats->sum_steps = sd.sum_steps, stats->best_lr = sd.best_lr, stats->members = ctx->stats_global ? ctx->pop_global : ctx->pop_local;
     }
     return LL_OK;
 }
@@ -579,10 +567,18 @@ extern "C" int ll_evaluate(ll_ctx* ctx, const int32_t* spad_x1, const int32_t* l
 extern "C" int ll_step_generation(ll_ctx* ctx, int32_t max_steps, int elitism, ll_gen_stats* stats)
 {
     LL_CHECK_CTX(ctx);
-    if (ctx->world != 1) return ll_fail(ctx, LL_EINVAL, "ll_step_generation is single-shard");
+    if (ctx->world != 1 && !ctx->comm) return ll_fail(ctx, LL_EINVAL, "ll_step_generation on a shard needs a communicator (ll_comm_init)");
     LL_TRY(ll_evaluate_device(ctx, max_steps));
-    LL_TRY(device_topk(ctx, (unsigned int)ctx->top));
-    LL_TRY(install_elites_from_idx(ctx, (unsigned int)ctx->top));
+    if (ctx->world == 1)
+    {
+        LL_TRY(device_topk(ctx, (unsigned int)ctx->top));
+        LL_TRY(install_elites_from_idx(ctx, (unsigned int)ctx->top));
+    }
+    else
+    { // K2 -> NCCL all-gather -> merge -> K3 -> NCCL all-reduce, all on the context's stream: no host round trip
+        scope s(ctx, CLS_SELECT, 1 + 12 + 1 + 1 + 4);
+        LL_TRY(ll_comm_select(ctx, false));
+    }
     {
         scope s(ctx, CLS_MUTATE, 1);
         LL_TRY(ll_launch_create_population_gen(ctx, elitism, ctx->epochs + 1));
@@ -782,6 +778,7 @@ extern "C" int ll_deserialize(ll_ctx* ctx, const char* path)
     if (rc != LL_OK) return ll_fail(ctx, rc, err);
     if (s != ctx->sizes) return ll_fail(ctx, LL_EINVAL, "ll_deserialize: the file's vSize does not match this context's topology");
     if (t != ctx->top) return ll_fail(ctx, LL_EINVAL, "ll_deserialize: the file's nTop does not match this context");
+    if (p != ctx->pop_global) return ll_fail(ctx, LL_EINVAL, "ll_deserialize: the file's nPopSize does not match this context's population");
     if (a != ctx->topo.activation) return ll_fail(ctx, LL_EINVAL, "ll_deserialize: the file's act does not match this context");
     const size_t pd = (size_t)ctx->topo.p_dev, pc = (size_t)ctx->topo.p_canon;
     const std::vector<int>& d2c = d2c_of(ctx);

@@ -389,6 +389,13 @@ namespace
                     const volatile double* all = a.part + member * (size_t)C * 4;
                     double f = 0.0, st = 0.0, s0 = 0.0, s1 = 0.0;
                     for (int c = 0; c < C; ++c) f += all[c * 4 + 0], st += all[c * 4 + 1], s0 += all[c * 4 + 2], s1 += all[c * 4 + 3];
+                    if (a.ep_fit)
+                    { // the chunk count depends on how many members this GPU holds: sum the per-episode values in LAYOUT order instead, so
+                      // that a small population's fitness is bit-identical for any GPU count (the exact kernel's order, :518)
+                        const volatile double* ef = a.ep_fit + member * (size_t)LT;
+                        f = 0.0;
+                        for (int l = 0; l < a.n_layouts; ++l) f += ef[l];
+                    }
                     fit_sum = f, steps_sum = (unsigned int)st, succ0 = (unsigned int)s0, succ1 = (unsigned int)s1;
                     a.part_count[member] = 0u;
                 }

@@ -124,8 +124,23 @@ struct ll_ctx
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     ll_kernel_times times = {};
 
+    // host copy of dev2canon and the CUDA-event profiling state live WITH the context (one host thread per context, any number of
+    // contexts per process: the multi-GPU trainer drives one context per thread)
+    std::vector<int> d2c;
+    struct ll_prof_holder* prof = nullptr;
+
+    // multi-rank exchange owned by the context (ll_comm.cu): NCCL communicator + scratch
+    void* comm = nullptr;            // ncclComm_t
+    ll_cand* d_cand_all = nullptr;   // [world * top] gathered candidates
+    double* d_red = nullptr;         // [4] all-reduce scratch: sum fitness, sum steps, lr of the best (owner only), unused
+    bool stats_global = false;       // d_stats holds whole-population statistics (after a communicator-backed selection)
+
     std::string err;
 };
+
+// multi-rank selection behind the ABI (ll_comm.cu)
+int ll_comm_select(ll_ctx* ctx, bool indices_given); // local top-k -> all-gather -> merge -> gather rows -> all-reduce; fills d_elites
+void ll_comm_release(ll_ctx* ctx);
 
 // ---- error plumbing ------------------------------------------------------------------------------------------
 void ll_set_error(ll_ctx* ctx, const std::string& msg);

@@ -95,6 +95,21 @@ class Engine:
             check(lib.ll_select(self._h, _p(s, C.c_uint64), len(s), _p(out, C.c_uint64)), self._h)
         return out
 
+    # ---- the exchange between GPUs, owned by the context (include/ll_gpu.h: ll_comm_*)
+    @staticmethod
+    def comm_unique_id() -> bytes:
+        buf = C.create_string_buffer(128)
+        check(lib.ll_comm_get_unique_id(buf))
+        return buf.raw
+
+    def comm_init(self, unique_id: bytes):
+        if len(unique_id) != 128:
+            raise ValueError("comm_init: the id is LL_COMM_ID_BYTES = 128 bytes")
+        check(lib.ll_comm_init(self._h, C.c_char_p(unique_id)), self._h)
+
+    def comm_destroy(self):
+        check(lib.ll_comm_destroy(self._h), self._h)
+
     def local_topk(self) -> Tuple[np.ndarray, np.ndarray]:
         buf = (_abi.Cand * self.top)()
         n = C.c_uint64()

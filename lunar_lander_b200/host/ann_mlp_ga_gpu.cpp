@@ -1,7 +1,9 @@
 #include "ann_mlp_ga_gpu.h"
 
 #include <cstdio>
+#include <exception>
 #include <stdexcept>
+#include <thread>
 #include <type_traits>
 
 #include "config_loader.h"
@@ -20,19 +22,57 @@ namespace nn
 
     template <typename T> void ANN_MLP_GA<T>::close()
     {
-        if (ctx_) ll_destroy(ctx_);
+        for (ll_ctx* c : ctxs_)
+            if (c) ll_destroy(c);
+        ctxs_.clear(), first_.clear();
         ctx_ = nullptr;
     }
 
-    template <typename T> void ANN_MLP_GA<T>::raise(const char* what) const
+    template <typename T> void ANN_MLP_GA<T>::raise_on(ll_ctx* ctx, const char* what) const
     {
-        const char* why = ll_last_error(ctx_);
+        const char* why = ll_last_error(ctx);
         throw std::runtime_error(std::string(what) + ": " + (why && *why ? why : "unknown error"));
     }
+    template <typename T> void ANN_MLP_GA<T>::raise(const char* what) const { raise_on(ctx_, what); }
 
     template <typename T> void ANN_MLP_GA<T>::require() const
     {
         if (!ctx_) throw std::runtime_error("ANN_MLP_GA: the network has no shape yet (construct with sizes or Deserialize first)");
+    }
+
+    // f(rank) for every shard.  One GPU: inline.  Several: one host thread per GPU for the duration of the call — the collectives
+    // inside the library (NCCL on each context's stream) need every rank to be in the same call at the same time.
+    template <typename T> template <class F> void ANN_MLP_GA<T>::each(F f) const
+    {
+        const size_t n = ctxs_.size();
+        if (n <= 1)
+        {
+            f(size_t(0));
+            return;
+        }
+        std::vector<std::exception_ptr> err(n);
+        std::vector<std::thread> th;
+        th.reserve(n);
+        for (size_t r = 0; r < n; ++r)
+            th.emplace_back([&, r] {
+                try
+                {
+                    f(r);
+                } catch (...)
+                {
+                    err[r] = std::current_exception();
+                }
+            });
+        for (auto& t : th) t.join();
+        for (auto& e : err)
+            if (e) std::rethrow_exception(e);
+    }
+
+    template <typename T> size_t ANN_MLP_GA<T>::owner_of(size_t member) const
+    {
+        for (size_t r = 0; r + 1 < first_.size(); ++r)
+            if (member >= first_[r] && member < first_[r + 1]) return r;
+        throw std::runtime_error("ANN_MLP_GA: member index out of range");
     }
 
     // The environment constants travel with the context (one copy instead of the reference's `pop` GameLogicCpp
@@ -49,40 +89,71 @@ namespace nn
                                                                   : Config::getStringOr("GpuCfg.mode", is_float ? "fast" : "exact");
         if (mode != "exact" && mode != "fast") throw std::runtime_error("GpuCfg.mode must be exact or fast, got " + mode);
         if (mode == "fast" && !is_float) throw std::runtime_error("GpuCfg.mode = fast needs the float build (main_train_f)");
-        ll_env_cfg env = Config::envCfg();
-        ll_net_cfg net{};
-        net.layer_sizes   = s.data();
-        net.n_layers      = static_cast<int32_t>(s.size());
-        net.activation_id = static_cast<int32_t>(act);
-        net.population    = pop;
-        net.top           = top;
-        net.seed          = seed;
-        net.precision     = is_float ? 32 : 64;
-        net.mode          = mode == "fast" ? LL_MODE_FAST : LL_MODE_EXACT;
-        net.rank          = 0;
-        net.world         = 1;
-        net.device        = Config::getIntOr("GpuCfg.device", 0);
-        net.sigma_init    = Config::getDoubleOr("GpuCfg.sigma_init", 0.0);
-        net.sigma_mut     = Config::getDoubleOr("GpuCfg.sigma_mut", 0.0);
-        if (ll_create(&ctx_, &env, &net) != LL_OK)
+        const int gpus = Config::getIntOr("GpuCfg.gpus", 1);
+        if (gpus < 1 || gpus > 64) throw std::runtime_error("GpuCfg.gpus must be in 1..64");
+        const int base    = Config::getIntOr("GpuCfg.device", 0);
+        ll_env_cfg env    = Config::envCfg();
+        ctxs_.assign(static_cast<size_t>(gpus), nullptr);
+        for (int r = 0; r < gpus; ++r)
         {
-            const char* why = ll_last_error(nullptr);
-            ctx_            = nullptr;
-            throw std::runtime_error(std::string("ANN_MLP_GA: ll_create failed: ") + (why ? why : "?"));
+            ll_net_cfg net{};
+            net.layer_sizes   = s.data();
+            net.n_layers      = static_cast<int32_t>(s.size());
+            net.activation_id = static_cast<int32_t>(act);
+            net.population    = pop;
+            net.top           = top;
+            net.seed          = seed;
+            net.precision     = is_float ? 32 : 64;
+            net.mode          = mode == "fast" ? LL_MODE_FAST : LL_MODE_EXACT;
+            net.rank          = r;
+            net.world         = gpus;
+            net.device        = base + r;
+            net.sigma_init    = Config::getDoubleOr("GpuCfg.sigma_init", 0.0);
+            net.sigma_mut     = Config::getDoubleOr("GpuCfg.sigma_mut", 0.0);
+            if (ll_create(&ctxs_[static_cast<size_t>(r)], &env, &net) != LL_OK)
+            {
+                const char* why       = ll_last_error(nullptr);
+                const std::string msg = std::string("ANN_MLP_GA: ll_create failed: ") + (why ? why : "?");
+                ctxs_[static_cast<size_t>(r)] = nullptr;
+                close();
+                throw std::runtime_error(msg);
+            }
         }
-        if (strategy_set_ && ll_set_population_strategy(ctx_, strategy_, ratio_) != LL_OK) raise("SetPopulationStrategy");
+        ctx_ = ctxs_[0];
+        first_.clear();
+        for (ll_ctx* c : ctxs_)
+        {
+            ll_info info{};
+            if (ll_get_info(c, &info) != LL_OK) raise_on(c, "ll_get_info");
+            first_.push_back(info.first_global);
+        }
+        first_.push_back(pop);
+        if (gpus > 1)
+        {
+            unsigned char id[LL_COMM_ID_BYTES];
+            if (ll_comm_get_unique_id(id) != LL_OK) raise_on(nullptr, "ll_comm_get_unique_id");
+            each([&](size_t r) {
+                if (ll_comm_init(ctxs_[r], id) != LL_OK) raise_on(ctxs_[r], "ll_comm_init");
+            });
+        }
+        if (strategy_set_)
+            for (ll_ctx* c : ctxs_)
+                if (ll_set_population_strategy(c, strategy_, ratio_) != LL_OK) raise_on(c, "SetPopulationStrategy");
     }
 
     template <typename T> void ANN_MLP_GA<T>::SetPopulationStrategy(PopulationStrategy strategy, double ratio)
     {
         strategy_ = static_cast<int>(strategy), ratio_ = ratio, strategy_set_ = true;
-        if (ctx_ && ll_set_population_strategy(ctx_, strategy_, ratio_) != LL_OK) raise("SetPopulationStrategy");
+        for (ll_ctx* c : ctxs_)
+            if (ll_set_population_strategy(c, strategy_, ratio_) != LL_OK) raise_on(c, "SetPopulationStrategy");
     }
 
     template <typename T> void ANN_MLP_GA<T>::CreatePopulation(bool elitism)
     {
         require();
-        if (ll_create_population(ctx_, elitism ? 1 : 0) != LL_OK) raise("CreatePopulation");
+        each([&](size_t r) {
+            if (ll_create_population(ctxs_[r], elitism ? 1 : 0) != LL_OK) raise_on(ctxs_[r], "CreatePopulation");
+        });
     }
 
     template <typename T> void ANN_MLP_GA<T>::UpdateWeightsAndBiases(const std::vector<size_t>& sorted_indices)
@@ -91,21 +162,26 @@ namespace nn
         if (sorted_indices.size() < top_) throw std::runtime_error("UpdateWeightsAndBiases: fewer indices than top performers");
         // only the first `top` entries matter (the parents); the rest of the order is never looked at
         std::vector<uint64_t> head(sorted_indices.begin(), sorted_indices.begin() + static_cast<long>(top_));
-        if (ll_select(ctx_, head.data(), head.size(), nullptr) != LL_OK) raise("UpdateWeightsAndBiases");
+        each([&](size_t r) {
+            if (ll_select(ctxs_[r], head.data(), head.size(), nullptr) != LL_OK) raise_on(ctxs_[r], "UpdateWeightsAndBiases");
+        });
     }
 
     template <typename T> std::vector<size_t> ANN_MLP_GA<T>::SelectOnDevice()
     {
         require();
         std::vector<uint64_t> idx(top_);
-        if (ll_select(ctx_, nullptr, 0, idx.data()) != LL_OK) raise("SelectOnDevice");
+        each([&](size_t r) {
+            if (ll_select(ctxs_[r], nullptr, 0, r == 0 ? idx.data() : nullptr) != LL_OK) raise_on(ctxs_[r], "SelectOnDevice");
+        });
         return std::vector<size_t>(idx.begin(), idx.end());
     }
 
     template <typename T> void ANN_MLP_GA<T>::UpdateEpochs(size_t n)
     {
         require();
-        if (ll_update_epochs(ctx_, n) != LL_OK) raise("UpdateEpochs");
+        for (ll_ctx* c : ctxs_)
+            if (ll_update_epochs(c, n) != LL_OK) raise_on(c, "UpdateEpochs");
     }
 
     template <typename T> size_t ANN_MLP_GA<T>::GetEpochs() const
@@ -119,7 +195,7 @@ namespace nn
     template <typename T> void ANN_MLP_GA<T>::Serialize(const std::string& path)
     {
         require();
-        if (ll_serialize(ctx_, path.c_str(), name_.c_str(), 6) != LL_OK) raise("Serialize");
+        if (ll_serialize(ctx_, path.c_str(), name_.c_str(), 6) != LL_OK) raise("Serialize"); // every rank holds the parent set
     }
 
     // The file decides the shape (sizes, population, top, activation, strategy), as in the reference where load()
@@ -141,7 +217,9 @@ namespace nn
         strategy_ = strategy, ratio_ = ratio, strategy_set_ = true;
         open(s, seed_ ? seed_ : static_cast<uint64_t>(static_cast<uint32_t>(Config::getIntOr("NNConfig.seed", 0))), pop, top,
              static_cast<size_t>(act));
-        if (ll_deserialize(ctx_, path.c_str()) != LL_OK) raise("Deserialize");
+        each([&](size_t r) { // every rank reads the parent set and rebuilds its own slots (Philox keyed by global member)
+            if (ll_deserialize(ctxs_[r], path.c_str()) != LL_OK) raise_on(ctxs_[r], "Deserialize");
+        });
         if (*stored_name) name_ = stored_name;
     }
 
@@ -150,7 +228,8 @@ namespace nn
         require();
         if (!inputs || n_inputs < sizes_.front()) throw std::runtime_error("feedforward: input buffer shorter than the input layer");
         uint64_t action = 0;
-        if (ll_feedforward_index(ctx_, inputs, member, &action) != LL_OK) raise("feedforward");
+        ll_ctx* c       = ctxs_[owner_of(member)];
+        if (ll_feedforward_index(c, inputs, member, &action) != LL_OK) raise_on(c, "feedforward");
         return static_cast<size_t>(action);
     }
 
@@ -161,8 +240,9 @@ namespace nn
         require();
         if (spad_x1.size() != lpad_x1.size() || spad_x1.size() != directions.size())
             throw std::runtime_error("SetLayouts: the three layout arrays differ in length");
-        if (ll_set_layouts(ctx_, spad_x1.data(), lpad_x1.data(), directions.data(), static_cast<int32_t>(spad_x1.size())) != LL_OK)
-            raise("SetLayouts");
+        for (ll_ctx* c : ctxs_)
+            if (ll_set_layouts(c, spad_x1.data(), lpad_x1.data(), directions.data(), static_cast<int32_t>(spad_x1.size())) != LL_OK)
+                raise_on(c, "SetLayouts");
     }
 
     template <typename T>
@@ -173,26 +253,46 @@ namespace nn
         require();
         if (spad_x1.size() != lpad_x1.size() || spad_x1.size() != directions.size())
             throw std::runtime_error("EvaluateGeneration: the three layout arrays differ in length");
-        if (ll_evaluate(ctx_, spad_x1.data(), lpad_x1.data(), directions.data(), static_cast<int32_t>(spad_x1.size()), max_steps,
-                        fitness, last_gen_lr, steps, stats) != LL_OK)
-            raise("EvaluateGeneration");
+        std::vector<ll_gen_stats> st(ctxs_.size());
+        each([&](size_t r) { // every shard writes its own slice of the caller's population-sized vectors
+            const uint64_t f = first_[r];
+            if (ll_evaluate(ctxs_[r], spad_x1.data(), lpad_x1.data(), directions.data(), static_cast<int32_t>(spad_x1.size()), max_steps,
+                            fitness ? fitness + f : nullptr, last_gen_lr ? last_gen_lr + f : nullptr, steps ? steps + f : nullptr,
+                            &st[r]) != LL_OK)
+                raise_on(ctxs_[r], "EvaluateGeneration");
+        });
+        if (stats)
+        { // whole-population statistics: best by (fitness, index), sums in rank order
+            *stats = st[0];
+            for (size_t r = 1; r < st.size(); ++r)
+            {
+                const bool better = st[r].best_fitness < stats->best_fitness ||
+                                    (st[r].best_fitness == stats->best_fitness && st[r].best_index < stats->best_index);
+                if (better) stats->best_fitness = st[r].best_fitness, stats->best_index = st[r].best_index, stats->best_lr = st[r].best_lr;
+                stats->sum_fitness += st[r].sum_fitness, stats->sum_steps += st[r].sum_steps, stats->members += st[r].members;
+            }
+        }
     }
 
     template <typename T> void ANN_MLP_GA<T>::StepGeneration(int max_steps, bool elitism, ll_gen_stats* stats)
     {
         require();
-        if (ll_step_generation(ctx_, max_steps, elitism ? 1 : 0, stats) != LL_OK) raise("StepGeneration");
+        each([&](size_t r) { // with several GPUs the statistics a rank reads back already describe the whole population
+            if (ll_step_generation(ctxs_[r], max_steps, elitism ? 1 : 0, r == 0 ? stats : nullptr) != LL_OK) raise_on(ctxs_[r], "StepGeneration");
+        });
     }
 
     template <typename T> void ANN_MLP_GA<T>::GetMember(size_t member, T* params) const
     {
         require();
-        if (ll_get_member(ctx_, member, params) != LL_OK) raise("GetMember");
+        ll_ctx* c = ctxs_[owner_of(member)];
+        if (ll_get_member(c, member, params) != LL_OK) raise_on(c, "GetMember");
     }
     template <typename T> void ANN_MLP_GA<T>::SetMember(size_t member, const T* params)
     {
         require();
-        if (ll_set_member(ctx_, member, params) != LL_OK) raise("SetMember");
+        ll_ctx* c = ctxs_[owner_of(member)];
+        if (ll_set_member(c, member, params) != LL_OK) raise_on(c, "SetMember");
     }
     template <typename T> size_t ANN_MLP_GA<T>::ParamCount() const
     {
@@ -205,7 +305,12 @@ namespace nn
     {
         require();
         double total = 0.0;
-        if (ll_step_counter(ctx_, &total, nullptr, reset ? 1 : 0) != LL_OK) raise("TotalLanderSteps");
+        for (ll_ctx* c : ctxs_)
+        {
+            double t = 0.0;
+            if (ll_step_counter(c, &t, nullptr, reset ? 1 : 0) != LL_OK) raise_on(c, "TotalLanderSteps");
+            total += t;
+        }
         return total;
     }
     template <typename T> std::string ANN_MLP_GA<T>::KernelName() const

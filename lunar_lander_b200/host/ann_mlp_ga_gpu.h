@@ -65,6 +65,10 @@ namespace nn
         double TotalLanderSteps(bool reset);
         std::string KernelName() const;
         ll_ctx* Context() const { return ctx_; }
+        // GpuCfg.gpus = N shards the population over N GPUs of this box: one context and one host thread per GPU, the exchange between
+        // them (NCCL) is owned by the contexts (ll_comm_init) — the GPU-side counterpart of the reference's per-member thread pool
+        // (src/nn_engine_trainer.cpp:460-538)
+        int Gpus() const { return static_cast<int>(ctxs_.size()); }
         // LL_MODE_EXACT / LL_MODE_FAST for the next open (constructor with sizes or Deserialize); default: GpuCfg.mode
         void SetMode(int mode) { mode_override_ = mode; }
 
@@ -74,7 +78,13 @@ namespace nn
         void require() const;
         [[noreturn]] void raise(const char* what) const;
 
-        ll_ctx* ctx_ = nullptr;
+        template <class F> void each(F f) const; // f(rank) on every shard, one host thread per GPU; rethrows the first failure
+        size_t owner_of(size_t member) const;
+        [[noreturn]] void raise_on(ll_ctx* ctx, const char* what) const;
+
+        ll_ctx* ctx_ = nullptr;        // rank 0's context (the only one when GpuCfg.gpus = 1)
+        std::vector<ll_ctx*> ctxs_;    // every rank's context
+        std::vector<uint64_t> first_;  // first GLOBAL member of every rank's shard, plus pop_ at the end
         std::vector<size_t> sizes_;
         size_t pop_ = 0, top_ = 0, act_ = LL_ACT_TANH;
         uint64_t seed_ = 0;

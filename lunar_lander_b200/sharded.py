@@ -5,8 +5,11 @@ needs no data-path collective; a generation has exactly two small exchanges:
   1. all-gather of every rank's `top` best (fitness, global index) pairs       -> global elite indices
   2. all-reduce (integer SUM over bit patterns == broadcast from the owners) of the [top][P] elite matrix
 
-Both go through ``torch.distributed`` (NCCL on GPUs, gloo in the CPU tests of the host logic).  The engine's
-kernels and the collectives are ordered on one CUDA stream (the engine is switched to torch's current stream).
+Both live BEHIND the C ABI (csrc/ll_comm.cu): the context owns the NCCL communicator, the candidate merge runs on the device and
+the whole generation (K1 -> K2 -> all-gather -> merge -> K3 -> all-reduce -> K4) is enqueued on the context's stream without a host
+round trip.  ``torch.distributed`` is used for one thing only: handing rank 0's 128-byte communicator id to the other processes.
+``pad_candidates`` / ``merge_candidates`` are the host statement of the merge order (what the device merge must reproduce); the CPU
+tests check them over gloo.
 """
 from __future__ import annotations
 
@@ -36,48 +39,30 @@ def merge_candidates(blocks: np.ndarray, top: int) -> Tuple[np.ndarray, np.ndarr
 
 
 class ShardedGeneration:
-    """evaluate -> select -> breed for one rank's shard, with the two exchanges above."""
+    """evaluate -> select -> breed for one rank's shard; the exchanges are the context's (ll_comm_init / ll_step_generation)."""
 
     def __init__(self, engine, group=None, device=None):
-        import torch
         import torch.distributed as dist
-        self.torch, self.dist = torch, dist
         self.eng, self.group = engine, group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
-        self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
-        n64 = engine.elite_buffer_bytes() // 8
-        self.elite_buf = torch.zeros(n64, dtype=torch.int64, device=self.device)
-        self.cand_local = torch.empty((engine.top, 2), dtype=torch.float64, device=self.device)
-        self.cand_all = torch.empty((self.world * engine.top, 2), dtype=torch.float64, device=self.device)
         self.h2d_bytes = 0
         self.d2h_bytes = 0
+        if self.world > 1:
+            box = [engine.comm_unique_id() if dist.get_rank(group) == 0 else None]
+            dist.broadcast_object_list(box, src=0, group=group)
+            engine.comm_init(box[0])
 
     def use_current_stream(self):
-        self.eng.set_stream(self.torch.cuda.current_stream().cuda_stream)
+        import torch
+        self.eng.set_stream(torch.cuda.current_stream().cuda_stream)
 
     def select_and_breed(self, elitism: bool = True) -> np.ndarray:
-        torch, dist, eng = self.torch, self.dist, self.eng
-        f, idx = eng.local_topk()                       # K2 on this shard (+ top x 16 B to the host)
-        self.d2h_bytes += 16 * len(f)
-        block = pad_candidates(f, idx, eng.top)
-        self.cand_local.copy_(torch.from_numpy(block), non_blocking=False)
-        self.h2d_bytes += block.nbytes
-        if self.world > 1:
-            dist.all_gather_into_tensor(self.cand_all, self.cand_local, group=self.group)
-        else:
-            self.cand_all.copy_(self.cand_local)
-        blocks = self.cand_all.cpu().numpy()
-        self.d2h_bytes += blocks.nbytes
-        _, elite_idx = merge_candidates(blocks, eng.top)
-        eng.gather_elites(elite_idx, self.elite_buf.data_ptr())  # K3: owned rows, zeros elsewhere
-        self.h2d_bytes += 8 * len(elite_idx)
-        if self.world > 1:
-            dist.all_reduce(self.elite_buf, op=dist.ReduceOp.SUM, group=self.group)
-        eng.set_elites(self.elite_buf.data_ptr())
-        eng.create_population(elitism)                   # K4 on this shard
-        eng.update_epochs(1)
+        elite_idx = self.eng.select(None)   # K2 -> NCCL all-gather -> device merge -> K3 -> NCCL all-reduce (+ top x 8 B to the host)
+        self.d2h_bytes += 8 * len(elite_idx)
+        self.eng.create_population(elitism)  # K4 on this shard
+        self.eng.update_epochs(1)
         return elite_idx
 
-    def step(self, max_steps: int, elitism: bool = True) -> np.ndarray:
-        self.eng.evaluate_device(max_steps)              # K1 (+ shard statistics)
-        return self.select_and_breed(elitism)
+    def step(self, max_steps: int, elitism: bool = True, want_stats: bool = False):
+        """one generation, nothing but (optionally) the statistics crosses PCIe"""
+        return self.eng.step_generation(max_steps, elitism, want_stats=want_stats)

@@ -176,3 +176,32 @@ def test_python_sharded_trainer_prints_the_cpp_trainer_log(tmp_path, built):
     assert files == sorted(os.listdir(os.path.join(b, "data"))) and "lunar_lander_last.txt" in files
     for name in files:
         assert open(os.path.join(a, "data", name)).read() == open(os.path.join(b, "data", name)).read(), name
+
+
+def _gpu_count():
+    import torch
+    return torch.cuda.device_count()
+
+
+@pytest.mark.parametrize("suffix,mode,select", [("d", "exact", "auto"), ("f", "exact", "auto"), ("f", "fast", "auto"), ("f", "exact", "device")])
+def test_cpp_trainer_on_two_gpus_prints_the_one_gpu_log(tmp_path, suffix, mode, select):
+    """GpuCfg.gpus = 2: the C++ mirror shards the population over two GPUs (one context + one host thread per GPU, NCCL owned by the
+    contexts: ll_comm_init, ll_select / ll_step_generation on shards).  Same config, same seeds -> the log and the checkpoint files
+    of the one-GPU run, bit for bit (exact mode) — selection order, children (Philox keyed by global member), statistics.
+    Runs only where two GPUs are visible (gpurun --gpus 2 and the driver's multi-GPU tier)."""
+    if _gpu_count() < 2:
+        pytest.skip("needs two GPUs")
+    ov = {"NNConfig.hlayers": "16,64,32", "NNConfig.epochs": 6, "NNConfig.population_size": 999, "NNTrainingCfg.layout_nb": 8,
+          "NNConfig.save_interval": 3, "GpuCfg.mode": mode, "GpuCfg.select": select}
+    one, two = str(tmp_path / "one"), str(tmp_path / "two")
+    write_config(one, **dict(ov, **{"GpuCfg.gpus": 1}))
+    write_config(two, **dict(ov, **{"GpuCfg.gpus": 2}))
+    r1 = run(os.path.join(BIN, "main_train_" + suffix), one)
+    r2 = run(os.path.join(BIN, "main_train_" + suffix), two)
+    assert r1[0] == 0, r1[2]
+    assert r2[0] == 0, r2[2]
+    assert normalise(r1[1]) == normalise(r2[1])
+    files = sorted(os.listdir(os.path.join(one, "data")))
+    assert files == sorted(os.listdir(os.path.join(two, "data"))) and files
+    for name in files:
+        assert weight_file_body(os.path.join(one, "data", name)) == weight_file_body(os.path.join(two, "data", name)), name
