@@ -519,10 +519,21 @@ extern "C" int ll_evaluate_device(ll_ctx* ctx, int32_t max_steps)
     return LL_OK;
 }
 
+// the tcgen05 episode kernel bounds every tensor-pipe wait and raises this flag (the word next to the work counter) instead of hanging
+static int check_kernel_flag(ll_ctx* ctx)
+{
+    unsigned int q[2] = {0u, 0u};
+    LL_CUDA(ctx, cudaMemcpyAsync(q, ctx->d_queue, sizeof(q), cudaMemcpyDeviceToHost, ctx->stream));
+    LL_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (q[1] != 0u) return ll_fail(ctx, LL_ECUDA, "episode kernel: a tensor-pipe wait timed out (results are invalid)");
+    return LL_OK;
+}
+
 extern "C" int ll_read_results(ll_ctx* ctx, double* fitness, double* last_gen_lr, double* steps, ll_gen_stats* stats)
 {
     LL_CHECK_CTX(ctx);
     if (!ctx->have_results) return ll_fail(ctx, LL_EINVAL, "ll_read_results: nothing evaluated yet");
+    LL_TRY(check_kernel_flag(ctx));
     const size_t n = ctx->pop_local * sizeof(double);
     LL_TRY(ensure_pinned(ctx, 3 * n + sizeof(ll_stats_dev)));
     char* h = static_cast<char*>(ctx->h_pin);

@@ -593,11 +593,22 @@ static bool ll_use_mmat(const ll_ctx* ctx, int n_layouts)
     return LL_MMAT_DEFAULT(n_layouts);
 }
 
+// the Blackwell tensor path (ll_episode_tc05.cu): tcgen05.mma, accumulators and activations in TMEM
+static bool ll_use_tc05(const ll_ctx* ctx, int n_layouts)
+{
+    if (!ll_tc05_applicable(ctx, n_layouts)) return false;
+    const char* force = getenv("LL_FAST_KERNEL");
+    if (force && !strcmp(force, "tc05")) return true;
+    if (force && *force) return false;
+    return LL_TC05_DEFAULT(ctx, n_layouts);
+}
+
 int ll_launch_episode(ll_ctx* ctx, const ll_episode_args& a)
 {
     if (ctx->precision == 64) return launch_t<double, LL_MODE_EXACT>(ctx, a);
     if (ctx->mode == LL_MODE_FAST)
     { // the team kernel needs weight reuse across layouts; traces and tiny layout counts stay lane-per-episode
+        if (a.trace == nullptr && ll_use_tc05(ctx, a.n_layouts)) return ll_launch_episode_tc05(ctx, a);
         if (a.trace == nullptr && ll_use_mmat(ctx, a.n_layouts)) return ll_launch_episode_mmat(ctx, a);
         if (a.trace == nullptr && ll_mma_applicable(ctx, a.n_layouts)) return ll_launch_episode_mma(ctx, a);
         if (a.trace == nullptr && ll_fast_applicable(ctx, a.n_layouts)) return ll_launch_episode_fast(ctx, a);
@@ -616,6 +627,7 @@ int ll_launch_feedforward(ll_ctx* ctx, const void* member_row, const void* d_sta
 const char* ll_episode_kernel_name(const ll_ctx* ctx, int n_layouts)
 {
     if (ctx->precision == 64) return "ll_episode_kernel<double,exact>";
+    if (ctx->mode == LL_MODE_FAST && ll_use_tc05(ctx, n_layouts)) return "ll_episode_tc05_kernel (3 x f16-split tcgen05.mma, TMEM activations)";
     if (ctx->mode == LL_MODE_FAST && ll_use_mmat(ctx, n_layouts)) return "ll_episode_mmat_kernel (3 x f16-split mma.sync, slots on N)";
     if (ctx->mode == LL_MODE_FAST && ll_mma_applicable(ctx, n_layouts)) return "ll_episode_mma_kernel (3 x f16-split mma.sync)";
     if (ctx->mode == LL_MODE_FAST) return ll_fast_applicable(ctx, n_layouts) ? "ll_episode_fast_kernel (slot-pool GEMM)" : "ll_episode_kernel<float,fast>";

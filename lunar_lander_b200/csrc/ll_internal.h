@@ -176,6 +176,11 @@ int ll_launch_episode_mma(ll_ctx* ctx, const ll_episode_args& a); // ll_episode_
 bool ll_mma_applicable(const ll_ctx* ctx, int n_layouts);
 int ll_launch_episode_mmat(ll_ctx* ctx, const ll_episode_args& a); // ll_episode_mmat.cu
 bool ll_mmat_applicable(const ll_ctx* ctx, int n_layouts);
+int ll_launch_episode_tc05(ll_ctx* ctx, const ll_episode_args& a); // ll_episode_tc05.cu
+bool ll_tc05_applicable(const ll_ctx* ctx, int n_layouts);
+// default choice of the tcgen05 kernel: off until it beats the mma.sync kernel on the benchmark workload; a population
+// must fill 6 members per SM for it to make sense
+#define LL_TC05_DEFAULT(ctx, n_layouts) (false)
 int ll_launch_feedforward(ll_ctx* ctx, const void* member_row, const void* d_state, unsigned long long* d_action);
 const char* ll_episode_kernel_name(const ll_ctx* ctx, int n_layouts);
 

@@ -116,6 +116,15 @@ namespace tc05
                      : "memory");
     }
 
+    __device__ __forceinline__ void st_x16(uint32_t taddr, const uint32_t (&v)[16])
+    {
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+                     :
+                     : "r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]),
+                       "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+                     : "memory");
+    }
+
     // ---- mbarrier ------------------------------------------------------------------------------------------------------
     __device__ __forceinline__ void mbar_init(uint32_t saddr, uint32_t count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" : : "r"(saddr), "r"(count) : "memory"); }
     __device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }

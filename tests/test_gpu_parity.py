@@ -637,3 +637,42 @@ def test_fast_mode_at_benchmark_size(ll, po, topo, pop, n_layouts):
     f2, l2, s2, _ = ex.evaluate(spad, lpad, d, 5000)
     assert np.array_equal(f2, want["fitness"]) and np.array_equal(s2, want["steps"]) and np.array_equal(l2, want["lr"])
     ex.close()
+
+
+@pytest.mark.parametrize("topo,n_layouts,pop", [("32_128_32", 50, 128), ("16_64_32", 33, 200), ("32_128_32", 64, 40), ("32_128_32", 17, 7)])
+def test_fast_tcgen05_kernel_tracks_exact_fp32(ll, po, topo, n_layouts, pop, monkeypatch):
+    """The Blackwell tensor-path episode kernel (ll_episode_tc05.cu: tcgen05.mma, accumulators and activations in TMEM, one thread per
+    slot) against the exact fp32 oracle and the mma.sync fast kernel on the same members — the bars of
+    test_fast_tensor_core_kernel_tracks_exact_fp32: >= 0.95 of the episodes end at the oracle's step, outcome flags >= 0.99,
+    >= 0.98 agreement with the mma.sync kernel; plus run-to-run determinism (fitness is summed in layout order)."""
+    members, sizes = util.elite_population(topo, pop, 4, noise=0.02)
+    members[pop // 2:] += util.random_population(sizes, pop - pop // 2, 8, scale=0.05)
+    spad, lpad, d = util.layouts(50)
+    if n_layouts > 50:
+        spad, lpad, d = np.tile(spad, 2), np.tile(lpad, 2), np.tile(d, 2)
+    spad, lpad, d = spad[:n_layouts], lpad[:n_layouts], d[:n_layouts]
+    got = {}
+    for kern in ("tc05", "tc05", "mma"):
+        monkeypatch.setenv("LL_FAST_KERNEL", kern)
+        eng, cfg = _engine(ll, sizes, pop, 32, mode=1)
+        eng.set_members(0, members)
+        fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
+        name = eng.info.kernel.decode()
+        assert ("_tc05_" in name) == (kern == "tc05"), name
+        ep_steps, flags, ep_fit = eng.read_episodes()
+        assert np.array_equal(steps, ep_steps.sum(axis=1).astype(np.float64))
+        assert st.sum_steps == steps.sum()
+        if kern == "tc05" and kern in got:
+            assert np.array_equal(got[kern][2], fit) and np.array_equal(got[kern][0], ep_steps)  # deterministic
+        got[kern] = (ep_steps, flags, fit, lr)
+        eng.close()
+    want = po.evaluate(cfg.env_cfg(), sizes, 1, members.astype(np.float32), spad, lpad, d, 5000, 32, threads=8)
+    ep_steps, flags, fit, lr = got["tc05"]
+    assert np.mean(ep_steps == want["ep_steps"]) >= 0.95
+    assert np.mean(flags == want["ep_flags"]) >= 0.99
+    assert np.mean(lr == want["lr"]) >= 0.9
+    assert np.mean(ep_steps == got["mma"][0]) >= 0.98
+    rows = np.all(ep_steps == want["ep_steps"], axis=1)
+    assert rows.any()
+    rel = np.abs(fit[rows] - want["fitness"][rows]) / np.maximum(1.0, np.abs(want["fitness"][rows]))
+    assert np.median(rel) <= 1e-5 and np.percentile(rel, 75) <= 1e-3, (np.median(rel), np.percentile(rel, 75), rel.max())
