@@ -173,7 +173,7 @@ namespace
 
     // tcgen05.mma chain of layer L for one half: D[64 x npad] (+)= X[64 x kpad] * W^T, three split products per K = 16 block.
     // tq = TMEM address of the quad's column 0 at the half's lane offset (0 or 16); sm = shared address of the member's region.
-    template <class N, int L> __device__ __forceinline__ void issue_layer(uint32_t tq, uint32_t sm)
+    template <class N, int L> __device__ __forceinline__ void issue_layer(uint32_t tq, uint32_t sm, int kc_begin = 0, int kc_end = N::kpad(L) / 16)
     {
         constexpr int KP = N::kpad(L), NP = N::npad(L);
         constexpr uint32_t idesc = tc05::idesc_f16(64, NP, 0, 0);
@@ -193,6 +193,7 @@ namespace
 #pragma unroll
             for (int kc = 0; kc < KP / 16; ++kc)
             {
+                if (kc < kc_begin || kc >= kc_end) continue;
                 const int k0 = 16 * kc;
                 const uint32_t a_hi = xin + (k0 / CH) * CH + (k0 % CH) / 2, a_lo = a_hi + CH / 2;
                 const uint64_t bhi = tc05::smem_desc(whi + 2 * kc * LBO, LBO, SBO), blo = tc05::smem_desc(wlo + 2 * kc * LBO, LBO, SBO);
@@ -201,6 +202,16 @@ namespace
                 tc05::mma_f16_ts(d, a_hi, bhi, idesc, 1u);
             }
         }
+    }
+
+    // issue layers L.. of both running halves, then commit; called by ONE elected lane of the quad's first warp
+    template <class N, int L>
+    __device__ __forceinline__ void issue_both(uint32_t tq, uint32_t sm0, bool run0, bool run1, uint32_t mbar, int kc_begin = 0, int kc_end = N::kpad(L) / 16,
+                                               bool last = true)
+    {
+        if (run0) issue_layer<N, L>(tq, sm0, kc_begin, kc_end);
+        if (run1) issue_layer<N, L>(tq + (16u << 16), sm0 + N::member_bytes, kc_begin, kc_end);
+        if (last) tc05::commit(mbar);
     }
 
     template <int CH> __device__ __forceinline__ void ld_chunk(uint32_t taddr, uint32_t (&v)[CH])
@@ -218,7 +229,11 @@ namespace
 
     // Hidden layer L, one thread = one slot: D row -> + bias -> tanh.approx -> f16 hi / lo -> back into the same TMEM columns as the
     // next layer's A operand (chunk c: hi words at column c*CH, lo words at c*CH + CH/2).
-    template <class N, int L> __device__ __forceinline__ void epilogue_hidden(uint32_t tt, const unsigned char* __restrict__ sm)
+    // PIPE: after every chunk the quad synchronises and one lane issues the next layer's K blocks that read this chunk, so that the
+    // tensor pipe works through layer L + 1 while the threads are still busy with the rest of layer L's activations.
+    template <class N, int L, bool PIPE>
+    __device__ __forceinline__ void epilogue_hidden(uint32_t tt, const unsigned char* __restrict__ sm, uint32_t tq = 0, uint32_t smq_a = 0, bool run0 = false,
+                                                    bool run1 = false, uint32_t mbar = 0, int q = 0, int wq = 0)
     {
         constexpr int NP = N::npad(L), CH = chunk_of<N>(L);
         const float4* sb = reinterpret_cast<const float4*>(sm + N::b_off(L));
@@ -241,6 +256,18 @@ namespace
             }
             st_words<CH / 2>(tt + N::dcol(L) + c * CH, hi);
             st_words<CH / 2>(tt + N::dcol(L) + c * CH + CH / 2, lo);
+            if constexpr (PIPE)
+            {
+                tc05::wait_st();
+                tc05::fence_before_sync();
+                tc05::named_bar_sync(1 + q, QUAD_THREADS);
+                tc05::fence_after_sync();
+                if (wq == 0)
+                {
+                    if (tc05::elect_one()) issue_both<N, L + 1>(tq, smq_a, run0, run1, mbar, c * (CH / 16), (c + 1) * (CH / 16), c + 1 == NP / CH);
+                    __syncwarp();
+                }
+            }
         }
     }
 
@@ -263,14 +290,6 @@ namespace
         const int by_smem = (227 * 1024 - 64) / (2 * N::member_bytes + (int)sizeof(quad_ctl));
         q = q < by_smem ? q : by_smem;
         return q > 3 ? 3 : (q < 1 ? 1 : q);
-    }
-
-    // issue layers L.. of both running halves, then commit; called by ONE elected lane of the quad's first warp
-    template <class N, int L> __device__ __forceinline__ void issue_both(uint32_t tq, uint32_t sm0, bool run0, bool run1, uint32_t mbar)
-    {
-        if (run0) issue_layer<N, L>(tq, sm0);
-        if (run1) issue_layer<N, L>(tq + (16u << 16), sm0 + N::member_bytes);
-        tc05::commit(mbar);
     }
 
     template <class N> struct step_loop;
@@ -390,31 +409,42 @@ namespace
     // Returns true when a bounded wait timed out.
     template <class N> struct step_loop
     {
-        template <int L>
+        // does layer L's epilogue issue layer L + 1 chunk by chunk?  (only worth a barrier per chunk where there are several chunks)
+        // Measured on B200 (32_128_32, 16 384 x 50): 175 ms with the per-chunk barriers against 163 ms without — a quad-wide bar.sync
+        // waits for the slowest of four warps that share their MUFU pipes with two other quads, which costs more than the overlap
+        // returns.  Off; kept because a dedicated issuer warp fed by mbarrier arrivals would make the same overlap free.
+        static constexpr bool PIPELINE = false;
+        template <int L> static __host__ __device__ constexpr bool pipelined() { return PIPELINE && L + 1 < N::NL && N::npad(L) / chunk_of<N>(L) > 1; }
+
+        template <int L, bool ISSUED = false>
         static __device__ __forceinline__ bool layers(const ll_env<float>& env, const tc_args& a, quad_ctl& ctl, uint32_t tq, uint32_t tt, uint32_t smq_a,
                                                       const unsigned char* smh, uint32_t mbar, int q, int wq, int h, int slot, bool run0, bool run1,
                                                       uint32_t& phase, ll_lander<float>& p, float cx, float lpad, float lpad_r, int& steps, double& acc,
                                                       bool& active)
         {
-            if constexpr (L > 0)
-            { // the activations this layer reads were written by every thread of the quad: order them before the issue
-                tc05::wait_st();
-                tc05::fence_before_sync();
-                tc05::named_bar_sync(1 + q, QUAD_THREADS);
-                tc05::fence_after_sync();
-            }
-            if (wq == 0)
+            if constexpr (!ISSUED)
             {
-                if (tc05::elect_one()) issue_both<N, L>(tq, smq_a, run0, run1, mbar);
-                __syncwarp();
+                if constexpr (L > 0)
+                { // the activations this layer reads were written by every thread of the quad: order them before the issue
+                    tc05::wait_st();
+                    tc05::fence_before_sync();
+                    tc05::named_bar_sync(1 + q, QUAD_THREADS);
+                    tc05::fence_after_sync();
+                }
+                if (wq == 0)
+                {
+                    if (tc05::elect_one()) issue_both<N, L>(tq, smq_a, run0, run1, mbar);
+                    __syncwarp();
+                }
             }
             if (!tc05::mbar_wait(mbar, phase)) return true;
             phase ^= 1u;
             tc05::fence_after_sync();
             if constexpr (L + 1 < N::NL)
             {
-                epilogue_hidden<N, L>(tt, smh);
-                return layers<L + 1>(env, a, ctl, tq, tt, smq_a, smh, mbar, q, wq, h, slot, run0, run1, phase, p, cx, lpad, lpad_r, steps, acc, active);
+                epilogue_hidden<N, L, pipelined<L>()>(tt, smh, tq, smq_a, run0, run1, mbar, q, wq);
+                return layers<L + 1, pipelined<L>()>(env, a, ctl, tq, tt, smq_a, smh, mbar, q, wq, h, slot, run0, run1, phase, p, cx, lpad, lpad_r, steps, acc,
+                                                     active);
             }
             else
             { // ---- output layer: tanh, argmax (first maximum wins), lander update + penalties, next state
