@@ -163,7 +163,7 @@ extern "C" void ll_destroy(ll_ctx* ctx)
     ll_comm_release(ctx);
     void* ptrs[] = {ctx->d_params, ctx->d_elites,   ctx->d_dev2canon, ctx->d_layouts, ctx->d_fitness, ctx->d_lr,        ctx->d_steps,
                     ctx->d_ep_steps, ctx->d_ep_fit, ctx->d_queue,     ctx->d_stats,   ctx->d_partials, ctx->d_sel,      ctx->d_keys,
-                    ctx->d_cand,   ctx->d_elite_idx, ctx->d_trace,    ctx->d_scratch, ctx->d_sim, ctx->d_part};
+                    ctx->d_cand,   ctx->d_elite_idx, ctx->d_trace,    ctx->d_scratch, ctx->d_sim, ctx->d_part, ctx->d_resume};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (ctx->h_pin) cudaFreeHost(ctx->h_pin);

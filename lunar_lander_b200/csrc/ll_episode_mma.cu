@@ -414,6 +414,124 @@ namespace
         }
     }
 
+    // ---- straggler pass behind the tcgen05 tile kernel (ll_episode_tc05.cu): a member's last <= 16 running episodes, handed over with
+    // their lander state, step count and accumulated step penalty, finish here in ONE 16-row tile (no refill: nothing is left to
+    // start).  The warp then closes the member: every layout's result, the tile kernel's and ours, is summed in layout order from the
+    // per-episode arrays (src/nn_engine_trainer.cpp:518-530).
+    struct resume_args
+    {
+        mma_args m;
+        ll_resume_args r;
+    };
+
+    template <class N>
+    __global__ void __launch_bounds__(32 * max_warps<N>(), 1) ll_episode_mma_resume_kernel(const __grid_constant__ ll_env<float> env, const __grid_constant__ resume_args ra)
+    {
+        const mma_args& a = ra.m;
+        extern __shared__ __align__(16) float smem_all[];
+        float* sw = smem_all + (threadIdx.x >> 5) * N::total;
+        const int lane = threadIdx.x & 31;
+        const int g = lane >> 2, t = lane & 3;
+        const int slot   = lane & 15;
+        const bool owner = lane < 16;
+        const int LT     = a.n_layouts;
+        for (int i = lane; i < N::total; i += 32) sw[i] = 0.f;
+        __syncwarp();
+        const unsigned int n_items = *ra.r.n;
+        for (;;)
+        {
+            unsigned int item = 0;
+            if (lane == 0) item = atomicAdd(a.queue, 1u);
+            item = __shfl_sync(0xffffffffu, item, 0);
+            if (item >= n_items) break;
+            const unsigned long long member = ra.r.list[item];
+            const int cnt                   = (int)ra.r.count[member];
+            __syncwarp();
+            stage_layer<N, 0>(a, a.params + member * (size_t)a.p_dev, sw, lane);
+            __syncwarp();
+            ll_lander<float> p{0.f, 0.f, 0.f, 0.f, 0.f};
+            float cx = 0.f, lpad = 0.f, lpad_r = 0.f;
+            int steps = 0, layout = 0;
+            double acc  = 0.0;
+            bool active = false;
+            if (slot < cnt)
+            {
+                const ll_resume_rec r = ra.r.rec[member * LL_RESUME_SLOTS + slot];
+                layout                = r.layout;
+                const ll_layout<float> lay = a.layouts[layout];
+                cx = lay.center_x, lpad = lay.lpad_x1, lpad_r = lay.lpad_right;
+                p      = ll_lander<float>{r.x, r.y, r.vx, r.vy, r.fuel};
+                steps = r.steps, acc = r.acc, active = true;
+            }
+            while (__ballot_sync(0xffffffffu, active) != 0u)
+            {
+                float st[5];
+                ll_get_state<float, LL_MODE_FAST>(env, p, cx, st, 1);
+                uint32_t a0h[1][4], a0l[1][4];
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+                {
+                    const int src = 8 * h + g;
+                    const float v0 = __shfl_sync(0xffffffffu, st[0], src), v1 = __shfl_sync(0xffffffffu, st[1], src);
+                    const float v2 = __shfl_sync(0xffffffffu, st[2], src), v3 = __shfl_sync(0xffffffffu, st[3], src);
+                    const float v4 = __shfl_sync(0xffffffffu, st[4], src);
+                    const float e0 = t == 0 ? v0 : (t == 1 ? v2 : (t == 2 ? v4 : 0.f));
+                    const float e1 = t == 0 ? v1 : (t == 1 ? v3 : 0.f);
+                    split_pair(e0, e1, a0h[0][h], a0l[0][h]);
+                    a0h[0][2 + h] = 0u, a0l[0][2 + h] = 0u;
+                }
+                float z[4];
+                chain<N, 0>::run(sw, lane, t, a0h, a0l, z);
+                unsigned packed = 0;
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+                {
+                    float best = z[2 * h];
+                    int idx    = 2 * t;
+                    if (z[2 * h + 1] > best) best = z[2 * h + 1], idx = 2 * t + 1;
+                    const float ob = __shfl_xor_sync(0xffffffffu, best, 1);
+                    const int oi   = __shfl_xor_sync(0xffffffffu, idx, 1);
+                    if (ob > best) idx = oi;
+                    packed |= (unsigned)idx << (4 * h);
+                }
+                const unsigned pk = __shfl_sync(0xffffffffu, packed, 4 * (slot & 7));
+                const int action  = (pk >> (4 * (slot >> 3))) & 15;
+                if (active)
+                {
+                    bool landed = false, success = false;
+                    float dist  = 0.f;
+                    const float sp = ll_env_step<float, LL_MODE_FAST>(env, p, action, steps == 0, cx, lpad, lpad_r, &landed, &success, &dist);
+                    acc += (double)sp;
+                    ++steps;
+                    if (landed || steps >= a.max_steps)
+                    {
+                        const float term = ll_terminal_penalty<float, LL_MODE_FAST>(env, p, steps, landed, success, dist);
+                        if (owner)
+                        {
+                            a.ep_steps[member * (size_t)LT + layout] = steps | (landed ? (1 << 28) : 0) | ((landed && !success) ? (1 << 29) : 0) | (success ? (1 << 30) : 0);
+                            a.ep_fit[member * (size_t)LT + layout]   = (double)term + acc;
+                        }
+                        active = false;
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0)
+            { // close the member: all layouts in layout order (the tile kernel wrote the others before this kernel started)
+                double f = 0.0, stp = 0.0;
+                float bonus0 = 0.f, bonus1 = 0.f;
+                for (int l = 0; l < LT; ++l)
+                {
+                    const int meta = a.ep_steps[member * (size_t)LT + l];
+                    f += a.ep_fit[member * (size_t)LT + l], stp += (double)(meta & 0x0fffffff);
+                    if (meta & (1 << 30)) (a.layouts[l].dir == 0 ? bonus0 : bonus1) += env.tp_landed_lr_bonus;
+                }
+                const double lr   = (double)(bonus1 < bonus0 ? bonus1 : bonus0);
+                a.fitness[member] = f - lr, a.lr[member] = lr, a.steps[member] = stp;
+            }
+        }
+    }
+
     int env_int(const char* name, int fallback)
     {
         const char* v = getenv(name);
@@ -512,4 +630,43 @@ int ll_launch_episode_mma(ll_ctx* ctx, const ll_episode_args& a)
     if (same_net<net_16_32>(tp)) return launch_mma_t<net_16_32>(ctx, a);
     if (same_net<net_16_16>(tp)) return launch_mma_t<net_16_16>(ctx, a);
     return ll_fail(ctx, LL_EINVAL, "mma episode kernel: topology not instantiated");
+}
+
+namespace
+{
+    template <class N> int launch_resume_t(ll_ctx* ctx, const ll_episode_args& h, const ll_resume_args& r)
+    {
+        const ll_topo& tp = ctx->topo;
+        resume_args ra{};
+        mma_args& a = ra.m;
+        a.params = static_cast<const float*>(h.params), a.layouts = static_cast<const ll_layout<float>*>(h.layouts);
+        a.n_layouts = h.n_layouts, a.max_steps = h.max_steps, a.n_members = h.n_members;
+        a.fitness = h.fitness, a.lr = h.lr, a.steps = h.steps, a.ep_steps = h.ep_steps, a.ep_fit = h.ep_fit;
+        a.queue = h.queue + 2; // the tile kernel uses words 0 (work counter) and 1 (error flag)
+        a.p_dev = tp.p_dev, a.chunks = 1;
+        for (int l = 0; l < tp.n_layers; ++l) a.w_off[l] = tp.w_off[l], a.b_off[l] = tp.b_off[l], a.out_pad[l] = tp.out_pad[l];
+        ra.r      = r;
+        auto kern = ll_episode_mma_resume_kernel<N>;
+        int max_smem = 0;
+        LL_CUDA(ctx, cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device));
+        const int warps = std::max(1, std::min<int>(max_warps<N>(), max_smem / (N::total * 4)));
+        const size_t smem = (size_t)warps * N::total * 4;
+        LL_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ll_env<float> env;
+        ll_make_env<float>(ctx->env_cfg, 1, &env);
+        LL_CUDA(ctx, cudaMemsetAsync(a.queue, 0, sizeof(unsigned int), ctx->stream));
+        const unsigned long long ctas_needed = (h.n_members + warps - 1) / warps;
+        const unsigned int grid = (unsigned int)std::max<unsigned long long>(1, std::min<unsigned long long>((unsigned long long)ctx->sm_count, ctas_needed));
+        kern<<<grid, 32 * warps, smem, ctx->stream>>>(env, ra);
+        LL_CUDA(ctx, cudaGetLastError());
+        return LL_OK;
+    }
+} // namespace
+
+int ll_launch_episode_mma_resume(ll_ctx* ctx, const ll_episode_args& a, const ll_resume_args& r)
+{
+    const ll_topo& tp = ctx->topo;
+    if (same_net<net_32_128_32>(tp)) return launch_resume_t<net_32_128_32>(ctx, a, r);
+    if (same_net<net_16_64_32>(tp)) return launch_resume_t<net_16_64_32>(ctx, a, r);
+    return ll_fail(ctx, LL_EINVAL, "mma resume kernel: topology not instantiated");
 }

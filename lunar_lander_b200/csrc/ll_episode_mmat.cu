@@ -33,9 +33,6 @@
 #define LL_MMAT_PANEL 8 /* output tiles of a layer processed together (their accumulator tiles and weight fragments live in registers) */
 #endif
 
-#ifndef LL_MMAT_MEMBERS_DEFAULT
-#define LL_MMAT_MEMBERS_DEFAULT 0
-#endif
 
 namespace
 {
@@ -261,7 +258,7 @@ namespace
     template <class N, int NT> constexpr int t_max_warps()
     {
         const int by_smem = (227 * 1024) / (N::total * 4);
-        if (NT == 1) return by_smem >= 16 ? 16 : (by_smem < 1 ? 1 : by_smem);
+        if (NT == 1) return by_smem >= 28 ? 28 : (by_smem >= 16 ? 16 : (by_smem < 1 ? 1 : by_smem));
         return by_smem >= 12 ? 12 : (by_smem >= 8 ? 8 : (by_smem < 1 ? 1 : by_smem)); // two tiles per warp need > 128 registers
     }
 
@@ -459,8 +456,6 @@ namespace
         }
     }
 
-#include "ll_episode_mmatm.inc"
-
     int t_env_int(const char* name, int fallback)
     {
         const char* v = getenv(name);
@@ -494,46 +489,9 @@ namespace
         return LL_OK;
     }
 
-    template <class N, int NT> int launch_mmatm_t(ll_ctx* ctx, const ll_episode_args& h)
-    {
-        const ll_topo& tp = ctx->topo;
-        mmat_args a{};
-        a.params = static_cast<const float*>(h.params), a.layouts = static_cast<const ll_layout<float>*>(h.layouts);
-        a.n_layouts = h.n_layouts, a.max_steps = h.max_steps, a.n_members = h.n_members;
-        a.fitness = h.fitness, a.lr = h.lr, a.steps = h.steps, a.ep_steps = h.ep_steps, a.ep_fit = h.ep_fit, a.queue = h.queue;
-        a.p_dev = tp.p_dev;
-        for (int l = 0; l < tp.n_layers; ++l) a.w_off[l] = tp.w_off[l], a.b_off[l] = tp.b_off[l], a.out_pad[l] = tp.out_pad[l];
-        auto kern = ll_episode_mmatm_kernel<N, NT>;
-        int max_smem = 0;
-        LL_CUDA(ctx, cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device));
-        const int warp_bytes = m_warp_words<N, NT>() * 4;
-        int warps = std::min<int>(m_max_warps<N, NT>(), max_smem / warp_bytes);
-        warps     = std::min(warps, t_env_int("LL_MMA_WARPS_PER_SM", warps));
-        if (warps < 1) return ll_fail(ctx, LL_EINVAL, "mmat episode kernel: the member rows do not fit in shared memory");
-        const size_t smem = (size_t)warps * warp_bytes;
-        LL_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        const unsigned long long per_cta = (unsigned long long)warps * NT;
-        const unsigned long long ctas_needed = (h.n_members + per_cta - 1) / per_cta;
-        const unsigned int grid = (unsigned int)std::max<unsigned long long>(1, std::min<unsigned long long>((unsigned long long)ctx->sm_count, ctas_needed));
-        ll_env<float> env;
-        ll_make_env<float>(ctx->env_cfg, 1, &env);
-        LL_CUDA(ctx, cudaMemsetAsync(h.queue, 0, sizeof(unsigned int), ctx->stream));
-        kern<<<grid, 32 * warps, smem, ctx->stream>>>(env, a);
-        LL_CUDA(ctx, cudaGetLastError());
-        return LL_OK;
-    }
-
-    // up to 8 layouts: LL_MMAT_MEMBERS members per warp, one 8-slot tile each (0 = one member per warp, the kernel above);
-    // beyond: one member per warp with one or two tiles
+    // one member per warp with one 8-slot tile (up to 8 layouts) or two
     template <class N> int launch_mmat(ll_ctx* ctx, const ll_episode_args& h)
     {
-        if (h.n_layouts <= 8)
-        {
-            const int nm = t_env_int("LL_MMAT_MEMBERS", LL_MMAT_MEMBERS_DEFAULT);
-            if (nm == 2) return launch_mmatm_t<N, 2>(ctx, h);
-            if (nm == 3) return launch_mmatm_t<N, 3>(ctx, h);
-            if (nm == 4) return launch_mmatm_t<N, 4>(ctx, h);
-        }
         const int nt = t_env_int("LL_MMAT_TILES", h.n_layouts <= 8 ? 1 : 2);
         return nt == 1 ? launch_mmat_t<N, 1>(ctx, h) : launch_mmat_t<N, 2>(ctx, h);
     }

@@ -102,6 +102,8 @@ namespace
         double* ep_fit;
         unsigned int* queue;
         int* error; // set to 1 when a bounded wait timed out
+        ll_resume_args resume; // hand-over of a member's last episodes to the 16-row mma.sync kernel (rec == nullptr: off)
+        int cut;               // a member leaves the tile when at most this many of its episodes are still running
         int p_dev;
         int w_off[LL_MAX_LAYERS], b_off[LL_MAX_LAYERS], out_pad[LL_MAX_LAYERS]; // the HBM row layout (ll_topo)
     };
@@ -208,7 +210,7 @@ namespace
     template <class N, int L>
     __device__ __forceinline__ void issue_both(uint32_t tq, uint32_t sm0, bool run0, bool run1, uint32_t mbar, int kc_begin = 0, int kc_end = N::kpad(L) / 16,
                                                bool last = true)
-    {
+    { // one half after the other (alternating the halves K block by K block measured 3 % slower: 169 vs 163 ms)
         if (run0) issue_layer<N, L>(tq, sm0, kc_begin, kc_end);
         if (run1) issue_layer<N, L>(tq + (16u << 16), sm0 + N::member_bytes, kc_begin, kc_end);
         if (last) tc05::commit(mbar);
@@ -333,6 +335,7 @@ namespace
         int steps = 0;
         double acc = 0.0;
         bool active = false, failed = false;
+        unsigned long long cur_member = ~0ull; // the member this thread's half is flying (kept in a register: the leader replaces ctl.member)
         uint32_t phase = 0;
         const int L    = a.n_layouts; // <= SLOTS: slot s flies layout s
 
@@ -346,14 +349,38 @@ namespace
             tc05::named_bar_sync(1 + q, QUAD_THREADS);
             tc05::fence_after_sync();
             const unsigned lv = ctl.live[0] | ctl.live[1] | ctl.live[2] | ctl.live[3];
-            const bool live0 = (lv & 0xffffu) != 0u, live1 = (lv >> 16) != 0u;
-            const bool mine_live = h ? live1 : live0;
-            if ((!live0 && !ctl.exhausted[0]) || (!live1 && !ctl.exhausted[1]))
-            { // ---- rare path (once per member): a half has finished its member -> book it, take the next one from the queue
-                if (slot == 0 && !mine_live && !ctl.exhausted[h])
+            (void)lv;
+            // A tile runs until its member's LONGEST episode ends; measured on the benchmark population only 40-54 % of the 64 rows are
+            // live on average, and the last 16 episodes of a member hold a tenth of its steps but a third of its tile time
+            // (scripts/liveness.py).  So when at most `cut` episodes are left the half hands them to the 16-row mma.sync kernel
+            // (one warp = one member x 16 slots, launched behind this kernel) and takes the next member.
+            const int c0 = __popc(ctl.live[0] & 0xffffu) + __popc(ctl.live[1] & 0xffffu) + __popc(ctl.live[2] & 0xffffu) + __popc(ctl.live[3] & 0xffffu);
+            const int c1 = __popc(ctl.live[0] >> 16) + __popc(ctl.live[1] >> 16) + __popc(ctl.live[2] >> 16) + __popc(ctl.live[3] >> 16);
+            const bool leave0 = !ctl.exhausted[0] && c0 <= a.cut, leave1 = !ctl.exhausted[1] && c1 <= a.cut;
+            const bool mine_live = !(h ? leave1 : leave0);
+            if (leave0 || leave1)
+            { // ---- rare path (once per member): a half has finished (or hands over) its member -> book it, take the next one from the queue
+                const int mine_left = h ? c1 : c0;
+                if (!mine_live && active)
+                { // my episode moves: rank among the half's running slots, in slot order
+                    const unsigned long long member = cur_member;
+                    int rank = 0;
+                    for (int w = 0; w < wq; ++w) rank += __popc(h ? (ctl.live[w] >> 16) : (ctl.live[w] & 0xffffu));
+                    rank += __popc((h ? (ctl.live[wq] >> 16) : (ctl.live[wq] & 0xffffu)) & ((1u << (lane & 15)) - 1u));
+                    ll_resume_rec r;
+                    r.x = p.x, r.y = p.y, r.vx = p.vx, r.vy = p.vy, r.fuel = p.fuel, r.layout = slot, r.steps = steps, r.pad_ = 0, r.acc = acc;
+                    a.resume.rec[member * LL_RESUME_SLOTS + rank] = r;
+                    active = false;
+                }
+                if (slot == 0 && !mine_live)
                 {
-                    const unsigned long long done = ctl.member[h];
-                    if (done != ~0ull)
+                    const unsigned long long done = cur_member;
+                    if (done != ~0ull && mine_left > 0)
+                    { // the straggler pass finishes the member (it sums every layout's result, ours included, from the per-episode arrays)
+                        a.resume.count[done] = (unsigned int)mine_left;
+                        a.resume.list[atomicAdd(a.resume.n, 1u)] = (unsigned int)done;
+                    }
+                    else if (done != ~0ull)
                     { // member totals, summed in layout order (src/nn_engine_trainer.cpp:518-530; deterministic, shard-independent)
                         double f = 0.0, st = 0.0;
                         float bonus0 = 0.f, bonus1 = 0.f;
@@ -374,6 +401,7 @@ namespace
                 if (!mine_live && ctl.member[h] != ~0ull && !ctl.exhausted[h])
                 { // the 64 threads of the half: stage the new member's weights, start one episode per layout
                     const unsigned long long member = ctl.member[h];
+                    cur_member                      = member;
                     stage_layer<N, 0>(a, a.params + member * (size_t)a.p_dev, smh, slot);
                     steps = 0, acc = 0.0, active = slot < L;
                     const ll_layout<float> lay = a.layouts[active ? slot : 0];
@@ -393,7 +421,7 @@ namespace
             }
             const bool run0 = ctl.member[0] != ~0ull, run1 = ctl.member[1] != ~0ull;
             if (!run0 && !run1) break; // both halves drained
-            if (step_loop<N>::run(env, a, ctl, tq, tt, smq_a, smh, mbar, q, wq, h, slot, run0, run1, phase, p, cx, lpad, lpad_r, steps, acc, active))
+            if (step_loop<N>::run(env, a, ctl, tq, tt, smq_a, smh, mbar, q, wq, h, slot, run0, run1, phase, p, cx, lpad, lpad_r, steps, acc, active, cur_member))
             {
                 failed = true;
                 break;
@@ -420,7 +448,7 @@ namespace
         static __device__ __forceinline__ bool layers(const ll_env<float>& env, const tc_args& a, quad_ctl& ctl, uint32_t tq, uint32_t tt, uint32_t smq_a,
                                                       const unsigned char* smh, uint32_t mbar, int q, int wq, int h, int slot, bool run0, bool run1,
                                                       uint32_t& phase, ll_lander<float>& p, float cx, float lpad, float lpad_r, int& steps, double& acc,
-                                                      bool& active)
+                                                      bool& active, unsigned long long member)
         {
             if constexpr (!ISSUED)
             {
@@ -444,7 +472,7 @@ namespace
             {
                 epilogue_hidden<N, L, pipelined<L>()>(tt, smh, tq, smq_a, run0, run1, mbar, q, wq);
                 return layers<L + 1, pipelined<L>()>(env, a, ctl, tq, tt, smq_a, smh, mbar, q, wq, h, slot, run0, run1, phase, p, cx, lpad, lpad_r, steps, acc,
-                                                     active);
+                                                     active, member);
             }
             else
             { // ---- output layer: tanh, argmax (first maximum wins), lander update + penalties, next state
@@ -476,7 +504,6 @@ namespace
                         ctl.ep_fit[h][slot] = fit, ctl.ep_meta[h][slot] = meta;
                         if (a.ep_steps)
                         {
-                            const unsigned long long member = ctl.member[h];
                             a.ep_steps[member * (size_t)a.n_layouts + slot] = meta;
                             a.ep_fit[member * (size_t)a.n_layouts + slot]   = fit;
                         }
@@ -493,11 +520,19 @@ namespace
         static __device__ __forceinline__ bool run(const ll_env<float>& env, const tc_args& a, quad_ctl& ctl, uint32_t tq, uint32_t tt, uint32_t smq_a,
                                                    const unsigned char* smh, uint32_t mbar, int q, int wq, int h, int slot, bool run0, bool run1,
                                                    uint32_t& phase, ll_lander<float>& p, float cx, float lpad, float lpad_r, int& steps, double& acc,
-                                                   bool& active)
+                                                   bool& active, unsigned long long member)
         {
-            return layers<0>(env, a, ctl, tq, tt, smq_a, smh, mbar, q, wq, h, slot, run0, run1, phase, p, cx, lpad, lpad_r, steps, acc, active);
+            return layers<0>(env, a, ctl, tq, tt, smq_a, smh, mbar, q, wq, h, slot, run0, run1, phase, p, cx, lpad, lpad_r, steps, acc, active, member);
         }
     };
+
+    // LL_TC05_CUT: a member leaves its 64-row tile for the 16-row straggler kernel when at most this many episodes are still running
+    // (0 = never; default 16 = one mma.sync tile)
+    int env_cut()
+    {
+        const char* v = getenv("LL_TC05_CUT");
+        return v && *v ? atoi(v) : LL_RESUME_SLOTS;
+    }
 
     template <class N> int launch_tc05_t(ll_ctx* ctx, const ll_episode_args& h)
     {
@@ -509,7 +544,28 @@ namespace
         a.fitness = h.fitness, a.lr = h.lr, a.steps = h.steps, a.ep_steps = h.ep_steps, a.ep_fit = h.ep_fit, a.queue = h.queue;
         a.p_dev = tp.p_dev;
         for (int l = 0; l < tp.n_layers; ++l) a.w_off[l] = tp.w_off[l], a.b_off[l] = tp.b_off[l], a.out_pad[l] = tp.out_pad[l];
-        a.error = reinterpret_cast<int*>(h.queue + 1); // the work counter's neighbour: zeroed with it, read back by ll_evaluate_device's caller
+        a.error = reinterpret_cast<int*>(h.queue + 1); // the work counter's neighbour: zeroed with it, read back by ll_read_results
+        // hand-over to the 16-row mma.sync kernel (needs the per-episode arrays: that is where the two kernels' results meet)
+        const int cut = h.ep_steps && h.ep_fit ? std::max(0, std::min(env_cut(), LL_RESUME_SLOTS)) : 0;
+        a.cut         = cut;
+        if (cut > 0)
+        {
+            const size_t rec_bytes = (size_t)h.n_members * LL_RESUME_SLOTS * sizeof(ll_resume_rec), cnt_bytes = (size_t)h.n_members * sizeof(unsigned int);
+            const size_t need = rec_bytes + 2 * cnt_bytes + 64;
+            if (ctx->resume_cap < need)
+            {
+                if (ctx->d_resume) cudaFree(ctx->d_resume);
+                ctx->d_resume = nullptr, ctx->resume_cap = 0;
+                LL_CUDA(ctx, cudaMalloc(&ctx->d_resume, need));
+                ctx->resume_cap = need;
+            }
+            char* base      = static_cast<char*>(ctx->d_resume);
+            a.resume.rec    = reinterpret_cast<ll_resume_rec*>(base);
+            a.resume.count  = reinterpret_cast<unsigned int*>(base + rec_bytes);
+            a.resume.list   = reinterpret_cast<unsigned int*>(base + rec_bytes + cnt_bytes);
+            a.resume.n      = reinterpret_cast<unsigned int*>(base + rec_bytes + 2 * cnt_bytes);
+            LL_CUDA(ctx, cudaMemsetAsync(a.resume.n, 0, sizeof(unsigned int), ctx->stream));
+        }
         auto kern         = ll_episode_tc05_kernel<N>;
         const size_t smem = (size_t)2 * NQ * N::member_bytes + (size_t)NQ * sizeof(quad_ctl);
         LL_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -520,6 +576,7 @@ namespace
         LL_CUDA(ctx, cudaMemsetAsync(h.queue, 0, 2 * sizeof(unsigned int), ctx->stream));
         kern<<<grid, QUAD_THREADS * NQ, smem, ctx->stream>>>(env, a);
         LL_CUDA(ctx, cudaGetLastError());
+        if (cut > 0 && !getenv("LL_TC05_DEBUG_NORESUME")) return ll_launch_episode_mma_resume(ctx, h, a.resume); // debug switch: time the tile kernel alone (results incomplete)
         return LL_OK;
     }
 

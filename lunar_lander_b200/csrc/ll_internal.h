@@ -108,6 +108,8 @@ struct ll_ctx
     void* d_scratch = nullptr; // small scratch (feedforward state, episode result)
     void* d_part    = nullptr; // ll_episode_mma.cu: per-(member, chunk) partial sums + arrival counters (small populations)
     size_t part_cap = 0;
+    void* d_resume  = nullptr; // ll_episode_tc05.cu: hand-over records + per-member counts + member list
+    size_t resume_cap = 0;
     void* d_sim     = nullptr; // ll_sim.cu: the single stepped lander (state, view, penalties), allocated on first use
     bool sim_ready = false, sim_custom = false;
     double sim_lpad_x1 = 0.0, sim_init_x = 0.0;
@@ -176,11 +178,28 @@ int ll_launch_episode_mma(ll_ctx* ctx, const ll_episode_args& a); // ll_episode_
 bool ll_mma_applicable(const ll_ctx* ctx, int n_layouts);
 int ll_launch_episode_mmat(ll_ctx* ctx, const ll_episode_args& a); // ll_episode_mmat.cu
 bool ll_mmat_applicable(const ll_ctx* ctx, int n_layouts);
+// An episode handed from the tcgen05 tile kernel to the 16-row mma.sync kernel when only a few of a member's episodes are still
+// running (ll_episode_tc05.cu -> ll_episode_mma.cu): everything sim_task keeps per episode (src/nn_engine_trainer.cpp:486-511).
+struct ll_resume_rec
+{
+    float x, y, vx, vy, fuel;
+    int layout, steps, pad_;
+    double acc;
+};
+#define LL_RESUME_SLOTS 16
+struct ll_resume_args
+{
+    ll_resume_rec* rec;            // [n_members][LL_RESUME_SLOTS]
+    unsigned int* count;           // [n_members] records of the member (0: nothing handed over)
+    unsigned int* list;            // members with records, in arrival order
+    unsigned int* n;               // number of entries of `list`
+};
+int ll_launch_episode_mma_resume(ll_ctx* ctx, const ll_episode_args& a, const ll_resume_args& r); // ll_episode_mma.cu
 int ll_launch_episode_tc05(ll_ctx* ctx, const ll_episode_args& a); // ll_episode_tc05.cu
 bool ll_tc05_applicable(const ll_ctx* ctx, int n_layouts);
-// default choice of the tcgen05 kernel: off until it beats the mma.sync kernel on the benchmark workload; a population
-// must fill 6 members per SM for it to make sense
-#define LL_TC05_DEFAULT(ctx, n_layouts) (false)
+// default choice of the tcgen05 kernel: where it applies (17..64 layouts, the instantiated topologies) and the shard fills its 6 member
+// slots per SM; measured 1.18-1.25 x the mma.sync kernel on the benchmark workload together with the straggler hand-over
+#define LL_TC05_DEFAULT(ctx, n_layouts) ((ctx)->pop_local >= 6ull * (unsigned long long)(ctx)->sm_count)
 int ll_launch_feedforward(ll_ctx* ctx, const void* member_row, const void* d_state, unsigned long long* d_action);
 const char* ll_episode_kernel_name(const ll_ctx* ctx, int n_layouts);
 

@@ -149,6 +149,7 @@ namespace tc05
     // Returns false on time-out (~ 2^26 polls, seconds).
     __device__ __forceinline__ bool mbar_wait(uint32_t saddr, uint32_t parity)
     {
+#pragma unroll 1
         for (uint32_t spin = 0; spin < (1u << 26); ++spin)
             if (mbar_try_wait(saddr, parity)) return true;
         return false;

@@ -25,6 +25,8 @@ eng.mark_elites()
 eng.set_population_strategy(2 if os.environ.get("INJECT", "1") == "1" else 1, 0.35)
 eng.create_population(True)
 eng.set_layouts(spad, lpad, dirs)
+for g in range(int(os.environ.get("GENS", "0"))):  # evolve a few generations first: later populations have a wider spread of episode lengths
+    eng.step_generation(5000, True, want_stats=False)
 for r in range(repeats):
     eng.profile(True)
     eng.kernel_times(reset=True)

@@ -497,33 +497,6 @@ def test_fast_small_population_layouts_dealt_to_several_warps(ll, po, monkeypatc
         assert np.array_equal(g[2], g[3].sum(axis=1).astype(np.float64))
 
 
-@pytest.mark.parametrize("topo,n_layouts,pop", [("16_64_32", 8, 333), ("8_16_8", 1, 500), ("8_16_32_16_8", 5, 97), ("32_128_32", 8, 61)])
-def test_fast_several_members_per_warp(ll, po, topo, n_layouts, pop, monkeypatch):
-    """Up to 8 layouts: the transposed tensor-core kernel can fly LL_MMAT_MEMBERS members per warp, one 8-slot tile each (lane = slot
-    for the environment, tiles refilled from the queue independently).  Every episode goes through the same products and the same
-    environment code as with one member per warp: per-episode steps, flags and fitness are identical; member totals agree to
-    summation order."""
-    members, sizes = util.elite_population(topo, pop, 4, noise=0.02)
-    members[pop // 2:] += util.random_population(sizes, pop - pop // 2, 8, scale=0.05)
-    spad, lpad, d = util.layouts(50)
-    spad, lpad, d = spad[:n_layouts], lpad[:n_layouts], d[:n_layouts]
-    monkeypatch.setenv("LL_FAST_KERNEL", "mmat")
-    got = {}
-    for nm in ("0", "2", "3", "4"):
-        monkeypatch.setenv("LL_MMAT_MEMBERS", nm)
-        eng, cfg = _engine(ll, sizes, pop, 32, mode=1)
-        eng.set_members(0, members)
-        fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
-        assert "_mmat_" in eng.info.kernel.decode()
-        got[nm] = (fit, lr, steps) + tuple(eng.read_episodes())
-        eng.close()
-    base = got["0"]
-    for nm, r in got.items():
-        assert np.array_equal(r[3], base[3]) and np.array_equal(r[4], base[4]) and np.array_equal(r[5], base[5]), nm
-        assert np.array_equal(r[2], base[2]) and np.array_equal(r[1], base[1]), nm
-        assert np.allclose(r[0], base[0], rtol=1e-12, atol=1e-9), nm
-
-
 @pytest.mark.parametrize("kernel", ["mma", "mmat"])
 def test_fast_mode_constant_policies(ll, kernel, monkeypatch):
     """Constant-action networks do not depend on the forward arithmetic: the fast kernel must reproduce the reference-owned
@@ -652,8 +625,11 @@ def test_fast_tcgen05_kernel_tracks_exact_fp32(ll, po, topo, n_layouts, pop, mon
         spad, lpad, d = np.tile(spad, 2), np.tile(lpad, 2), np.tile(d, 2)
     spad, lpad, d = spad[:n_layouts], lpad[:n_layouts], d[:n_layouts]
     got = {}
-    for kern in ("tc05", "tc05", "mma"):
+    # tc05 = tile kernel + hand-over of a member's last <= 16 running episodes to the 16-row mma.sync kernel (the default);
+    # tc05_nocut = the tile kernel alone (LL_TC05_CUT=0)
+    for tag, kern, cut in (("tc05", "tc05", "16"), ("tc05", "tc05", "16"), ("tc05_nocut", "tc05", "0"), ("mma", "mma", "16")):
         monkeypatch.setenv("LL_FAST_KERNEL", kern)
+        monkeypatch.setenv("LL_TC05_CUT", cut)
         eng, cfg = _engine(ll, sizes, pop, 32, mode=1)
         eng.set_members(0, members)
         fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
@@ -662,10 +638,12 @@ def test_fast_tcgen05_kernel_tracks_exact_fp32(ll, po, topo, n_layouts, pop, mon
         ep_steps, flags, ep_fit = eng.read_episodes()
         assert np.array_equal(steps, ep_steps.sum(axis=1).astype(np.float64))
         assert st.sum_steps == steps.sum()
-        if kern == "tc05" and kern in got:
-            assert np.array_equal(got[kern][2], fit) and np.array_equal(got[kern][0], ep_steps)  # deterministic
-        got[kern] = (ep_steps, flags, fit, lr)
+        assert np.array_equal(fit + lr, ep_fit.sum(axis=1)) or np.allclose(fit + lr, ep_fit.sum(axis=1), rtol=1e-12)
+        if tag in got:
+            assert np.array_equal(got[tag][2], fit) and np.array_equal(got[tag][0], ep_steps)  # deterministic
+        got[tag] = (ep_steps, flags, fit, lr)
         eng.close()
+    assert np.mean(got["tc05"][0] == got["tc05_nocut"][0]) >= 0.98
     want = po.evaluate(cfg.env_cfg(), sizes, 1, members.astype(np.float32), spad, lpad, d, 5000, 32, threads=8)
     ep_steps, flags, fit, lr = got["tc05"]
     assert np.mean(ep_steps == want["ep_steps"]) >= 0.95
