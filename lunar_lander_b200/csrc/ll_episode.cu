@@ -589,7 +589,7 @@ static bool ll_use_mmat(const ll_ctx* ctx, int n_layouts)
     if (!ll_mmat_applicable(ctx, n_layouts)) return false;
     const char* force = getenv("LL_FAST_KERNEL");
     if (force && !strcmp(force, "mmat")) return true;
-    if (force && (!strcmp(force, "mma") || !strcmp(force, "ffma"))) return false;
+    if (force && *force) return false;
     return LL_MMAT_DEFAULT(n_layouts);
 }
 
@@ -603,11 +603,22 @@ static bool ll_use_tc05(const ll_ctx* ctx, int n_layouts)
     return LL_TC05_DEFAULT(ctx, n_layouts);
 }
 
+// warp per member, neurons across lanes (ll_episode_warp.cu): no weight reuse to exploit with one layout per member
+static bool ll_use_warp(const ll_ctx* ctx, int n_layouts)
+{
+    if (!ll_warp_applicable(ctx, n_layouts)) return false;
+    const char* force = getenv("LL_FAST_KERNEL");
+    if (force && !strcmp(force, "warp")) return true;
+    if (force && *force) return false;
+    return n_layouts <= LL_WARP_MAX_LAYOUTS;
+}
+
 int ll_launch_episode(ll_ctx* ctx, const ll_episode_args& a)
 {
     if (ctx->precision == 64) return launch_t<double, LL_MODE_EXACT>(ctx, a);
     if (ctx->mode == LL_MODE_FAST)
     { // the team kernel needs weight reuse across layouts; traces and tiny layout counts stay lane-per-episode
+        if (a.trace == nullptr && ll_use_warp(ctx, a.n_layouts)) return ll_launch_episode_warp(ctx, a);
         if (a.trace == nullptr && ll_use_tc05(ctx, a.n_layouts)) return ll_launch_episode_tc05(ctx, a);
         if (a.trace == nullptr && ll_use_mmat(ctx, a.n_layouts)) return ll_launch_episode_mmat(ctx, a);
         if (a.trace == nullptr && ll_mma_applicable(ctx, a.n_layouts)) return ll_launch_episode_mma(ctx, a);
@@ -627,6 +638,7 @@ int ll_launch_feedforward(ll_ctx* ctx, const void* member_row, const void* d_sta
 const char* ll_episode_kernel_name(const ll_ctx* ctx, int n_layouts)
 {
     if (ctx->precision == 64) return "ll_episode_kernel<double,exact>";
+    if (ctx->mode == LL_MODE_FAST && ll_use_warp(ctx, n_layouts)) return "ll_episode_warp_kernel (warp per member, FFMA + shuffles)";
     if (ctx->mode == LL_MODE_FAST && ll_use_tc05(ctx, n_layouts)) return "ll_episode_tc05_kernel (tcgen05.mma + TMEM, stragglers -> mma.sync)";
     if (ctx->mode == LL_MODE_FAST && ll_use_mmat(ctx, n_layouts)) return "ll_episode_mmat_kernel (3 x f16-split mma.sync, slots on N)";
     if (ctx->mode == LL_MODE_FAST && ll_mma_applicable(ctx, n_layouts)) return "ll_episode_mma_kernel (3 x f16-split mma.sync)";

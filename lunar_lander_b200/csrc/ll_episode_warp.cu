@@ -1,0 +1,200 @@
+// ll_episode_warp.cu — K1 fast for FEW layouts per member (BASELINE.json configs[1]: 8_16_8, population 4096, ONE start position).
+//
+// Replaces the same reference code as the other episode kernels: train_generation / sim_task src/nn_engine_trainer.cpp:443-539,
+// GameLogicCpp<T> src/game_logic.cpp:124-388 and the ma-libs feedforward call :501-502.
+//
+// With a single layout there is no weight reuse to turn the forward pass into a GEMM: the tensor-core kernels then pay a full 8- or
+// 16-slot tile for one live slot (configs[1]: 1 of 8 columns, ~930 cycles per lander step per warp).  This kernel is the mapping
+// BASELINE.json north_star (a) describes: ONE WARP = ONE MEMBER, the neurons of a layer across the lanes, the member's weights in
+// REGISTERS (lane j keeps row j of every layer: sum of the layer widths = 37 floats for 8_16_8), activations exchanged with warp
+// shuffles, the argmax taken in-warp, the lander state replicated in every lane (so the first layer needs no exchange and the
+// environment step no broadcast).  fp32 FFMA on unsplit weights, tanh.approx.f32: LL_MODE_FAST arithmetic, judged on outcomes.
+// A generation of configs[1] is as long as its longest episode (5000 dependent steps), so what counts is the latency of one step:
+// ~70 FFMA / SHFL pairs + 36 MUFU for 8_16_8 instead of 45 HMMA + 520 other instructions.
+// Supported: tanh networks whose layers are at most 32 wide (the sample_runs topologies 8_16_8, 16_16, 16_32, 8_16_32_16_8).
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+
+#include "ll_env.cuh"
+
+namespace
+{
+    template <int... S> struct wnet
+    {
+        static constexpr int NS = sizeof...(S);
+        static constexpr int NL = NS - 1;
+        static __host__ __device__ constexpr int sz(int i)
+        {
+            constexpr int a[NS] = {S...};
+            return a[i];
+        }
+        static __host__ __device__ constexpr int w_at(int l) // first register of layer l's weight row
+        {
+            int o = 0;
+            for (int i = 0; i < l; ++i) o += sz(i);
+            return o;
+        }
+        static constexpr int n_w = w_at(NL);
+        static __host__ __device__ constexpr bool ok()
+        {
+            for (int i = 0; i < NS; ++i)
+                if (sz(i) > 32) return false;
+            return sz(0) <= 5 && sz(NL) <= 4;
+        }
+    };
+
+    struct warp_args
+    {
+        const float* params;
+        const ll_layout<float>* layouts;
+        int n_layouts, max_steps;
+        unsigned long long n_members;
+        double *fitness, *lr, *steps;
+        int* ep_steps;
+        double* ep_fit;
+        unsigned int* queue;
+        int p_dev;
+        int w_off[LL_MAX_LAYERS], b_off[LL_MAX_LAYERS], out_pad[LL_MAX_LAYERS]; // the HBM row layout (ll_topo)
+    };
+
+    // layers L..NL-1 of the forward pass; x = this lane's activation of layer L's input (layer 0: the state, replicated in st)
+    template <class N, int L> __device__ __forceinline__ float forward(const float (&w)[N::n_w], const float (&b)[N::NL], const float (&st)[5], float x)
+    {
+        constexpr int IN = N::sz(L);
+        float acc0 = b[L], acc1 = 0.f; // two chains: the dependent FFMA latency is what a step is made of
+#pragma unroll
+        for (int k = 0; k < IN; ++k)
+        {
+            const float a = L == 0 ? st[k] : __shfl_sync(0xffffffffu, x, k);
+            if (k & 1) acc1 = fmaf(w[N::w_at(L) + k], a, acc1);
+            else acc0 = fmaf(w[N::w_at(L) + k], a, acc0);
+        }
+        const float y = ll_tanh_approx(acc0 + acc1);
+        if constexpr (L + 1 < N::NL) return forward<N, L + 1>(w, b, st, y);
+        else return y;
+    }
+
+    template <class N> __global__ void __launch_bounds__(256) ll_episode_warp_kernel(const __grid_constant__ ll_env<float> env, const __grid_constant__ warp_args a)
+    {
+        static_assert(N::ok(), "topology not supported by the warp-per-member episode kernel");
+        const int lane = threadIdx.x & 31;
+        for (;;)
+        {
+            unsigned long long member = 0;
+            if (lane == 0) member = (unsigned long long)atomicAdd(a.queue, 1u);
+            member = __shfl_sync(0xffffffffu, member, 0);
+            if (member >= a.n_members) break;
+            // ---- the member's weights: lane j <- row j of every layer (coalesced: the HBM row is k-major, Wt[k][out_pad])
+            const float* row = a.params + member * (size_t)a.p_dev;
+            float w[N::n_w], b[N::NL];
+#pragma unroll
+            for (int l = 0; l < N::NL; ++l)
+            {
+                const bool mine = lane < N::sz(l + 1);
+#pragma unroll
+                for (int k = 0; k < N::sz(l); ++k) w[N::w_at(l) + k] = mine ? __ldg(row + a.w_off[l] + k * a.out_pad[l] + lane) : 0.f;
+                b[l] = mine ? __ldg(row + a.b_off[l] + lane) : 0.f;
+            }
+            double fit_sum = 0.0, steps_sum = 0.0;
+            float bonus0 = 0.f, bonus1 = 0.f;
+            for (int layout = 0; layout < a.n_layouts; ++layout)
+            { // the layouts one after the other, like sim_task (:486): this kernel is for one or two of them
+                const ll_layout<float> lay = a.layouts[layout];
+                ll_lander<float> p{lay.init_x, env.y0, env.vx0, env.vy0, env.max_fuel};
+                const float cx = lay.center_x, lpad = lay.lpad_x1, lpad_r = lay.lpad_right;
+                int steps = 0;
+                double acc = 0.0;
+                bool landed = false, success = false;
+                float dist = 0.f;
+                while (steps < a.max_steps)
+                {
+                    float st[5];
+                    ll_get_state<float, LL_MODE_FAST>(env, p, cx, st, 1);
+                    const float z = forward<N, 0>(w, b, st, 0.f);
+                    // argmax over the outputs (first maximum wins), every lane computes it
+                    float best = __shfl_sync(0xffffffffu, z, 0);
+                    int action = 0;
+#pragma unroll
+                    for (int j = 1; j < N::sz(N::NL); ++j)
+                    {
+                        const float zj = __shfl_sync(0xffffffffu, z, j);
+                        if (zj > best) best = zj, action = j;
+                    }
+                    const float sp = ll_env_step<float, LL_MODE_FAST>(env, p, action, steps == 0, cx, lpad, lpad_r, &landed, &success, &dist);
+                    acc += (double)sp;
+                    ++steps;
+                    if (landed) break;
+                }
+                const float term = ll_terminal_penalty<float, LL_MODE_FAST>(env, p, steps, landed, success, dist);
+                const double fit = (double)term + acc;
+                fit_sum += fit, steps_sum += (double)steps;
+                if (success) (lay.dir == 0 ? bonus0 : bonus1) += env.tp_landed_lr_bonus;
+                if (a.ep_steps && lane == 0)
+                {
+                    a.ep_steps[member * (size_t)a.n_layouts + layout] = steps | (landed ? (1 << 28) : 0) | ((landed && !success) ? (1 << 29) : 0) | (success ? (1 << 30) : 0);
+                    a.ep_fit[member * (size_t)a.n_layouts + layout]   = fit;
+                }
+            }
+            if (lane == 0)
+            {
+                const double lr   = (double)(bonus1 < bonus0 ? bonus1 : bonus0);
+                a.fitness[member] = fit_sum - lr, a.lr[member] = lr, a.steps[member] = steps_sum;
+            }
+        }
+    }
+
+    template <class N> int launch_warp_t(ll_ctx* ctx, const ll_episode_args& h)
+    {
+        const ll_topo& tp = ctx->topo;
+        warp_args a{};
+        a.params = static_cast<const float*>(h.params), a.layouts = static_cast<const ll_layout<float>*>(h.layouts);
+        a.n_layouts = h.n_layouts, a.max_steps = h.max_steps, a.n_members = h.n_members;
+        a.fitness = h.fitness, a.lr = h.lr, a.steps = h.steps, a.ep_steps = h.ep_steps, a.ep_fit = h.ep_fit, a.queue = h.queue;
+        a.p_dev = tp.p_dev;
+        for (int l = 0; l < tp.n_layers; ++l) a.w_off[l] = tp.w_off[l], a.b_off[l] = tp.b_off[l], a.out_pad[l] = tp.out_pad[l];
+        // spread the members over the SMs first (a generation lasts as long as its longest episode: fewer warps per scheduler =
+        // shorter steps), 8 warps per block, persistent warps drawing members from the queue
+        int per_sm = 0;
+        LL_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ll_episode_warp_kernel<N>, 256, 0));
+        const unsigned long long resident = (unsigned long long)ctx->sm_count * std::max(1, per_sm);
+        const unsigned long long wanted   = (h.n_members + 7) / 8;
+        const unsigned int grid = (unsigned int)std::max<unsigned long long>(1, std::min(resident, wanted));
+        ll_env<float> env;
+        ll_make_env<float>(ctx->env_cfg, 1, &env);
+        LL_CUDA(ctx, cudaMemsetAsync(h.queue, 0, sizeof(unsigned int), ctx->stream));
+        ll_episode_warp_kernel<N><<<grid, 256, 0, ctx->stream>>>(env, a);
+        LL_CUDA(ctx, cudaGetLastError());
+        return LL_OK;
+    }
+
+    using wnet_16_16        = wnet<5, 16, 16, 4>;
+    using wnet_16_32        = wnet<5, 16, 32, 4>;
+    using wnet_8_16_8       = wnet<5, 8, 16, 8, 4>;
+    using wnet_8_16_32_16_8 = wnet<5, 8, 16, 32, 16, 8, 4>;
+
+    template <class N> bool same_net(const ll_topo& tp)
+    {
+        if (tp.n_layers != N::NL || tp.in[0] != N::sz(0)) return false;
+        for (int l = 0; l < N::NL; ++l)
+            if (tp.out[l] != N::sz(l + 1)) return false;
+        return true;
+    }
+} // namespace
+
+bool ll_warp_applicable(const ll_ctx* ctx, int n_layouts)
+{
+    const ll_topo& tp = ctx->topo;
+    if (tp.activation != LL_ACT_TANH || ctx->precision != 32 || ctx->mode != LL_MODE_FAST || n_layouts < 1) return false;
+    return same_net<wnet_16_16>(tp) || same_net<wnet_16_32>(tp) || same_net<wnet_8_16_8>(tp) || same_net<wnet_8_16_32_16_8>(tp);
+}
+
+int ll_launch_episode_warp(ll_ctx* ctx, const ll_episode_args& a)
+{
+    const ll_topo& tp = ctx->topo;
+    if (same_net<wnet_8_16_8>(tp)) return launch_warp_t<wnet_8_16_8>(ctx, a);
+    if (same_net<wnet_16_16>(tp)) return launch_warp_t<wnet_16_16>(ctx, a);
+    if (same_net<wnet_16_32>(tp)) return launch_warp_t<wnet_16_32>(ctx, a);
+    if (same_net<wnet_8_16_32_16_8>(tp)) return launch_warp_t<wnet_8_16_32_16_8>(ctx, a);
+    return ll_fail(ctx, LL_EINVAL, "warp-per-member episode kernel: topology not instantiated");
+}

@@ -200,6 +200,9 @@ bool ll_tc05_applicable(const ll_ctx* ctx, int n_layouts);
 // default choice of the tcgen05 kernel: where it applies (17..64 layouts, the instantiated topologies) and the shard fills its 6 member
 // slots per SM; measured 1.18-1.25 x the mma.sync kernel on the benchmark workload together with the straggler hand-over
 #define LL_TC05_DEFAULT(ctx, n_layouts) ((ctx)->pop_local >= 6ull * (unsigned long long)(ctx)->sm_count)
+int ll_launch_episode_warp(ll_ctx* ctx, const ll_episode_args& a); // ll_episode_warp.cu
+bool ll_warp_applicable(const ll_ctx* ctx, int n_layouts);
+#define LL_WARP_MAX_LAYOUTS 1 /* default choice of the warp-per-member kernel: a single layout per member (configs[1]) */
 int ll_launch_feedforward(ll_ctx* ctx, const void* member_row, const void* d_state, unsigned long long* d_action);
 const char* ll_episode_kernel_name(const ll_ctx* ctx, int n_layouts);
 

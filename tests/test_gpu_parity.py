@@ -654,3 +654,33 @@ def test_fast_tcgen05_kernel_tracks_exact_fp32(ll, po, topo, n_layouts, pop, mon
     assert rows.any()
     rel = np.abs(fit[rows] - want["fitness"][rows]) / np.maximum(1.0, np.abs(want["fitness"][rows]))
     assert np.median(rel) <= 1e-5 and np.percentile(rel, 75) <= 1e-3, (np.median(rel), np.percentile(rel, 75), rel.max())
+
+
+@pytest.mark.parametrize("topo,n_layouts,pop", [("8_16_8", 1, 4096), ("16_16", 2, 500), ("8_16_32_16_8", 1, 300), ("16_16", 3, 77)])
+def test_fast_warp_per_member_kernel(ll, po, topo, n_layouts, pop, monkeypatch):
+    """ll_episode_warp.cu (one warp = one member, neurons across lanes, weights in registers, shuffles: the configs[1] kernel) against the
+    exact fp32 oracle: unsplit fp32 weights and FFMA, so it tracks the oracle at least as closely as the tensor-core kernels
+    (>= 0.95 of the episodes end at the same step, flags >= 0.99); it is the default for a single layout per member."""
+    members, sizes = util.elite_population(topo, pop, 4, noise=0.02)
+    members[pop // 2:] += util.random_population(sizes, pop - pop // 2, 8, scale=0.05)
+    spad, lpad, d = util.layouts(50)
+    spad, lpad, d = spad[:n_layouts], lpad[:n_layouts], d[:n_layouts]
+    monkeypatch.setenv("LL_FAST_KERNEL", "warp")
+    eng, cfg = _engine(ll, sizes, pop, 32, mode=1)
+    eng.set_members(0, members)
+    fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
+    assert "_warp_" in eng.info.kernel.decode()
+    ep_steps, flags, ep_fit = eng.read_episodes()
+    eng.close()
+    assert np.array_equal(steps, ep_steps.sum(axis=1).astype(np.float64)) and st.sum_steps == steps.sum()
+    want = po.evaluate(cfg.env_cfg(), sizes, 1, members.astype(np.float32), spad, lpad, d, 5000, 32, threads=8)
+    assert np.mean(ep_steps == want["ep_steps"]) >= 0.95
+    assert np.mean(flags == want["ep_flags"]) >= 0.99
+    rows = np.all(ep_steps == want["ep_steps"], axis=1)
+    rel = np.abs(fit[rows] - want["fitness"][rows]) / np.maximum(1.0, np.abs(want["fitness"][rows]))
+    assert np.median(rel) <= 1e-5 and np.percentile(rel, 75) <= 1e-3
+    monkeypatch.delenv("LL_FAST_KERNEL")
+    eng, _ = _engine(ll, sizes, pop, 32, mode=1)
+    eng.set_layouts(spad, lpad, d)
+    assert ("_warp_" in eng.info.kernel.decode()) == (n_layouts == 1)
+    eng.close()
