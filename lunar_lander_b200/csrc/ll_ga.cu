@@ -76,6 +76,58 @@ namespace
         }
     }
 
+    // float populations: one block per member row, ONE THREAD = 4 consecutive device-order parameters = one Philox block, four
+    // Box-Muller variates in float (ll_normal4_f32), the parent's float4 (L2-resident), one 16-byte store.  No shared-memory staging,
+    // no fp64: the kernel is bound by the HBM write of the children instead of the ALU (the fp64 polar transform above: 10 % of HBM).
+    __global__ void __launch_bounds__(256) ll_create_population_f32_kernel(const __grid_constant__ pop_args a)
+    {
+        using O = exact_ops<float>;
+        __shared__ int s_inject, s_parent;
+        const int qpr = a.p_dev >> 2; // quads per row (p_dev is a multiple of 8)
+        const int4* d2c4 = reinterpret_cast<const int4*>(a.dev2canon);
+        const float s_init = (float)a.sigma_init, s_mut = (float)a.sigma_mut;
+        for (unsigned long long ml = blockIdx.x; ml < a.pop_local; ml += gridDim.x)
+        {
+            const unsigned long long mg = a.first_global + ml;
+            float4* row = reinterpret_cast<float4*>(static_cast<float*>(a.params) + ml * (size_t)a.p_dev);
+            if (a.from_elites && mg < a.first_child)
+            { // elitism: slot r keeps elite r unchanged
+                const float4* src = reinterpret_cast<const float4*>(static_cast<const float*>(a.elites) + mg * (size_t)a.p_dev);
+                for (int qd = threadIdx.x; qd < qpr; qd += blockDim.x) row[qd] = src[qd];
+                continue;
+            }
+            if (threadIdx.x == 0)
+            {
+                const bool inject = !a.from_elites || ll_is_injected(mg - a.first_child, a.n_children, a.n_inject);
+                s_inject = inject ? 1 : 0;
+                s_parent = inject ? 0 : (int)ll_parent_pick(a.seed, a.gen, (uint32_t)mg, a.top);
+            }
+            __syncthreads();
+            const bool inject   = s_inject != 0;
+            const float4* parent = reinterpret_cast<const float4*>(static_cast<const float*>(a.elites) + (size_t)s_parent * a.p_dev);
+            for (int qd = threadIdx.x; qd < qpr; qd += blockDim.x)
+            {
+                float g[4];
+                ll_normal4_f32(a.seed, a.gen, (uint32_t)mg, (uint32_t)qd, g);
+                const int4 c = d2c4[qd];
+                float4 v;
+                if (inject) v = make_float4(O::mul(s_init, g[0]), O::mul(s_init, g[1]), O::mul(s_init, g[2]), O::mul(s_init, g[3]));
+                else
+                {
+                    const float4 pr = parent[qd];
+                    v = make_float4(O::add(pr.x, O::mul(s_mut, g[0])), O::add(pr.y, O::mul(s_mut, g[1])), O::add(pr.z, O::mul(s_mut, g[2])),
+                                    O::add(pr.w, O::mul(s_mut, g[3])));
+                }
+                if (c.x < 0) v.x = 0.f; // padding columns of the forward layout stay zero
+                if (c.y < 0) v.y = 0.f;
+                if (c.z < 0) v.z = 0.f;
+                if (c.w < 0) v.w = 0.f;
+                row[qd] = v;
+            }
+            __syncthreads();
+        }
+    }
+
     // ------------------------------------------------------------------------------------------------ K2 stats
     // Deterministic two-level reduction: block b owns elements [b*CH, (b+1)*CH); partials are combined in block
     // order by the last kernel.  Ties on the minimum resolve to the lowest index.
@@ -336,8 +388,7 @@ int ll_launch_create_population_gen(ll_ctx* ctx, int elitism, uint64_t gen)
     }
     else
     {
-        LL_CUDA(ctx, cudaFuncSetAttribute(ll_create_population_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        ll_create_population_kernel<float><<<grid, 256, smem, ctx->stream>>>(a);
+        ll_create_population_f32_kernel<<<grid, 256, 0, ctx->stream>>>(a);
     }
     LL_CUDA(ctx, cudaGetLastError());
     return LL_OK;

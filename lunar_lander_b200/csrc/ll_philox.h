@@ -84,6 +84,110 @@ LL_UNROLL
     }
 }
 
+// ---- fp32 populations: four N(0,1) variates per Philox block, Box-Muller in float ------------------------------------------------
+// The fp64 transform above (polar method, ll_log in double) is what makes K4 ALU-bound at 10 % of the HBM roofline for a float
+// population; the float build needs no more than float normals.  Deterministic like the rest of this header: IEEE float +,-,*,/
+// and sqrt in a fixed order, no FMA, integer bit manipulation — bit-identical on host and device.
+//   block (quad, member, gen, LL_STREAM_NORMAL32): words (w0, w1) -> two variates, (w2, w3) -> two more; no rejection
+//   radius r = sqrt(-2 ln u), u = ((w >> 9) + 0.5) 2^-23 in (0, 1);  angle 2 pi t: quadrant = top two bits of the second word,
+//   t' = ((w >> 7 & 0x7fffff) + 0.5) 2^-23 of a quarter turn, folded onto [0, pi/4] where short Taylor polynomials are exact to 3e-8
+#define LL_STREAM_NORMAL32 0x02000000u
+#if defined(__CUDA_ARCH__)
+#define LL_FMUL(a, b) __fmul_rn((a), (b))
+#define LL_FADD(a, b) __fadd_rn((a), (b))
+#define LL_FSUB(a, b) __fsub_rn((a), (b))
+#define LL_FDIV(a, b) __fdiv_rn((a), (b))
+#define LL_FSQRT(a) __fsqrt_rn((a))
+#else
+#define LL_FMUL(a, b) ((a) * (b))
+#define LL_FADD(a, b) ((a) + (b))
+#define LL_FSUB(a, b) ((a) - (b))
+#define LL_FDIV(a, b) ((a) / (b))
+#define LL_FSQRT(a) sqrtf((a))
+#endif
+
+LL_HD uint32_t ll_f2u(float x)
+{
+#if defined(__CUDA_ARCH__)
+    return __float_as_uint(x);
+#else
+    uint32_t u;
+    memcpy(&u, &x, 4);
+    return u;
+#endif
+}
+LL_HD float ll_u2f(uint32_t u)
+{
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(u);
+#else
+    float x;
+    memcpy(&x, &u, 4);
+    return x;
+#endif
+}
+
+// ln(x) for a normal float x in (0, 1]: x = m 2^k with m in [sqrt(1/2), sqrt(2)), ln m = 2 atanh(s), s = (m - 1) / (m + 1), |s| < 0.1716
+LL_HD float ll_logf_det(float x)
+{
+    uint32_t ux   = ll_f2u(x);
+    int k         = (int)(ux >> 23) - 127;
+    uint32_t mant = ux & 0x007fffffu;
+    if (mant >= 0x003504f3u) k += 1, ux = mant | 0x3f000000u; // m >= sqrt(2): halve
+    else ux = mant | 0x3f800000u;
+    const float m = ll_u2f(ux);
+    const float s = LL_FDIV(LL_FSUB(m, 1.0f), LL_FADD(m, 1.0f));
+    const float z = LL_FMUL(s, s);
+    float q       = 0.11111111f;                     // 1/9   (next term s^11 / 11 < 4e-10)
+    q             = LL_FADD(LL_FMUL(q, z), 0.14285715f); // 1/7
+    q             = LL_FADD(LL_FMUL(q, z), 0.2f);        // 1/5
+    q             = LL_FADD(LL_FMUL(q, z), 0.33333334f); // 1/3
+    const float lm = LL_FMUL(2.0f, LL_FADD(s, LL_FMUL(LL_FMUL(s, z), q)));
+    return LL_FADD(LL_FMUL((float)k, 0.69314718f), lm);
+}
+
+// (r cos, r sin) of angle 2 pi (quadrant + t) / 4
+LL_HD void ll_box_muller_f32(uint32_t w_radius, uint32_t w_angle, float* n0, float* n1)
+{
+    const float u = LL_FMUL(LL_FADD((float)(w_radius >> 9), 0.5f), 1.1920929e-07f); // 2^-23
+    const float r = LL_FSQRT(LL_FMUL(-2.0f, ll_logf_det(u)));
+    const uint32_t quad = w_angle >> 30;
+    float t             = LL_FMUL(LL_FADD((float)((w_angle >> 7) & 0x007fffffu), 0.5f), 1.1920929e-07f); // (0, 1) of a quarter turn
+    const bool fold     = t > 0.5f;
+    if (fold) t = LL_FSUB(1.0f, t);
+    const float x = LL_FMUL(t, 1.5707964f), x2 = LL_FMUL(x, x); // [0, pi/4]
+    float sp      = 2.7557319e-06f;                                 // 1/9!
+    sp            = LL_FADD(LL_FMUL(sp, x2), -1.9841270e-04f);      // -1/7!
+    sp            = LL_FADD(LL_FMUL(sp, x2), 8.3333333e-03f);       // 1/5!
+    sp            = LL_FADD(LL_FMUL(sp, x2), -1.6666667e-01f);      // -1/3!
+    float sn      = LL_FADD(x, LL_FMUL(LL_FMUL(x, x2), sp));
+    float cp      = 2.4801587e-05f;                                 // 1/8!
+    cp            = LL_FADD(LL_FMUL(cp, x2), -1.3888889e-03f);      // -1/6!
+    cp            = LL_FADD(LL_FMUL(cp, x2), 4.1666667e-02f);       // 1/4!
+    cp            = LL_FADD(LL_FMUL(cp, x2), -0.5f);
+    float cs      = LL_FADD(1.0f, LL_FMUL(x2, cp));
+    if (fold)
+    { // sin(pi/2 - x) = cos x
+        const float tmp = sn;
+        sn = cs, cs = tmp;
+    }
+    float c = cs, s_ = sn; // rotate by the quadrant
+    if (quad == 1u) c = -sn, s_ = cs;
+    else if (quad == 2u) c = -cs, s_ = -sn;
+    else if (quad == 3u) c = sn, s_ = -cs;
+    *n0 = LL_FMUL(r, c);
+    *n1 = LL_FMUL(r, s_);
+}
+
+// Four N(0,1) variates for DEVICE-order positions [4 quad, 4 quad + 4) of global member `member` (the device row layout is a
+// function of the topology alone, so the draw does not depend on the GPU count or the launch geometry).
+LL_HD void ll_normal4_f32(uint32_t seed, uint32_t gen, uint32_t member, uint32_t quad, float* g)
+{
+    const ll_u32x4 w = ll_philox4x32_10(quad, member, gen, LL_STREAM_NORMAL32, seed, LL_KEY1);
+    ll_box_muller_f32(w.v[0], w.v[1], &g[0], &g[1]);
+    ll_box_muller_f32(w.v[2], w.v[3], &g[2], &g[3]);
+}
+
 // Parent (elite slot) of a mutated child: uniform in [0, top).
 LL_HD uint32_t ll_parent_pick(uint32_t seed, uint32_t gen, uint32_t member, uint32_t top)
 {

@@ -19,11 +19,13 @@
 #include <cstring>
 #include <numeric>
 #include <thread>
+#include <type_traits>
 #include <vector>
 
 #include "../include/ll_gpu.h"
 #include "ll_math.h"
 #include "ll_philox.h"
+#include "ll_devlayout.h"
 
 namespace
 {
@@ -306,11 +308,26 @@ namespace
         std::vector<T> elites;
         if (has_elites) elites.assign(params, params + top * P);
         const T s_init = static_cast<T>(sigma_init), s_mut = static_cast<T>(sigma_mut);
+        const std::vector<int> d2c = orc_dev2canon(sizes, n_sizes);
         for (uint64_t i = first; i < pop; ++i)
         {
             const bool inject = ll_is_injected(i - first, pop - first, n_inject);
             const T* parent   = inject ? nullptr : &elites[(size_t)ll_parent_pick(seed, gen, (uint32_t)i, (uint32_t)top) * P];
             T* dst            = params + i * P;
+            if (std::is_same<T, float>::value)
+            { // float populations: four Box-Muller variates per DEVICE-order quad (ll_normal4_f32), padding positions discarded
+                for (size_t qd = 0; qd * 4 < d2c.size(); ++qd)
+                {
+                    float g[4];
+                    ll_normal4_f32(seed, gen, (uint32_t)i, (uint32_t)qd, g);
+                    for (int e = 0; e < 4; ++e)
+                    {
+                        const int c = d2c[qd * 4 + e];
+                        if (c >= 0) dst[c] = inject ? s_init * (T)g[e] : parent[c] + s_mut * (T)g[e];
+                    }
+                }
+                continue;
+            }
             for (size_t j = 0; j < P; j += 2)
             {
                 double n0, n1;

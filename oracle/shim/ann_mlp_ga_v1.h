@@ -28,10 +28,12 @@
 #include <sstream>
 #include <stdexcept>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "ll_math.h"
 #include "ll_philox.h"
+#include "../ll_devlayout.h"
 
 namespace nn
 {
@@ -292,6 +294,8 @@ namespace nn
             std::vector<T> elites;
             if (from_elites) elites.assign(params_.begin(), params_.begin() + static_cast<long>(top_ * P_));
             const T s_init = static_cast<T>(sigma_init), s_mut = static_cast<T>(sigma_mut);
+            std::vector<uint64_t> sz64(sizes_.begin(), sizes_.end());
+            const std::vector<int> d2c = orc_dev2canon(sz64.data(), static_cast<int>(sz64.size()));
             for (size_t i = first; i < pop_; ++i)
             {
                 const bool inject = ll_is_injected(i - first, n_children, n_inject);
@@ -299,6 +303,21 @@ namespace nn
                 if (!inject)
                     parent = &elites[ll_parent_pick(seed_, gen, static_cast<uint32_t>(i), static_cast<uint32_t>(top_)) * P_];
                 T* dst = &params_[i * P_];
+                if (std::is_same<T, float>::value)
+                { // float populations: four Box-Muller variates per DEVICE-order quad (ll_normal4_f32), padding positions discarded
+                    for (size_t qd = 0; qd * 4 < d2c.size(); ++qd)
+                    {
+                        float g[4];
+                        ll_normal4_f32(seed_, gen, static_cast<uint32_t>(i), static_cast<uint32_t>(qd), g);
+                        for (int e = 0; e < 4; ++e)
+                        {
+                            const int c = d2c[qd * 4 + e];
+                            if (c >= 0) dst[c] = inject ? s_init * static_cast<T>(g[e]) : parent[c] + s_mut * static_cast<T>(g[e]);
+                        }
+                    }
+                    rebuild_forward(i);
+                    continue;
+                }
                 for (size_t j = 0; j < P_; j += 2)
                 {
                     double n0, n1;

@@ -274,3 +274,26 @@ def test_create_population_statistics(built):
     # generation / seed / member all change the draw; the same key reproduces it
     assert not np.array_equal(p1, po.create_population(sizes, 5247, pop, top, 2, 2, 0.35, True, True, 1.0, 0.1, p0))
     assert np.array_equal(p1, po.create_population(sizes, 5247, pop, top, 1, 2, 0.35, True, True, 1.0, 0.1, p0))
+
+
+def test_float_population_draws_are_standard_normal(built):
+    """fp32 populations draw their Gaussians in float (ll_normal4_f32: Philox block -> two Box-Muller pairs with deterministic float
+    log / sin / cos, csrc/ll_philox.h): moments, tails and independence of the four variates of a block."""
+    import pyoracle as po
+    from scipy import stats
+    sizes = util.TOPOLOGIES["16_64_32"]
+    P = util.param_count(sizes)
+    pop = 300
+    p0 = po.create_population(sizes, 5247, pop, 10, 0, 2, 0.35, True, False, 1.0, 0.1, np.zeros((pop, P)), 32).astype(np.float64)
+    x = p0.ravel()
+    assert abs(x.mean()) < 4.0 / np.sqrt(x.size) and abs(x.std() - 1.0) < 5e-3
+    assert abs(stats.skew(x)) < 0.02 and abs(stats.kurtosis(x)) < 0.03
+    assert stats.kstest(x[:200000], "norm").pvalue > 1e-3
+    assert np.abs(x).max() < 6.5 and (np.abs(x) > 4).mean() < 2e-4          # radius from 23-bit uniforms: |x| <= sqrt(-2 ln 2^-24) = 5.77
+    c = np.corrcoef(p0[:, :-1].ravel(), p0[:, 1:].ravel())[0, 1]          # neighbouring parameters (same Philox block or the next)
+    assert abs(c) < 0.01
+    p1 = po.create_population(sizes, 5247, pop, 10, 3, 2, 0.35, True, True, 1.0, 0.1, p0, 32)
+    fresh = util.injected_mask(pop, 10, 0.35)
+    kids = (p1[10:][~fresh[10:]]).astype(np.float64)
+    d = np.abs(kids[:, None, :] - p0[None, :10, :]).mean(axis=2).min(axis=1)
+    assert d.max() < 0.15 and d.min() > 0.05                               # children = parent + N(0, 0.1^2): E|d| = 0.08
