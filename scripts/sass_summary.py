@@ -12,7 +12,7 @@ LIB = os.path.join(ROOT, "lunar_lander_b200", "libll_gpu.so")
 WANT = [("tc05_32_128_32", r"ll_episode_tc05_kernel.*Li5ELi32ELi128ELi32ELi4E"), ("mma_resume_32_128_32", r"ll_episode_mma_resume_kernel.*Li5ELi32ELi128ELi32ELi4E"),
         ("mma_32_128_32", r"ll_episode_mma_kernel.*Li5ELi32ELi128ELi32ELi4E.*Li0E"), ("mmat_16_64_32", r"ll_episode_mmat_kernel.*Li5ELi16ELi64ELi32ELi4E.*Li1E"),
         ("warp_8_16_8", r"ll_episode_warp_kernel.*Li5ELi8ELi16ELi8ELi4E"), ("exact_f64", r"ll_episode_kernel.*IdLi0E"),
-        ("create_population_f32", r"ll_create_population.*If")]
+        ("create_population_f32", r"ll_create_population_f32_kernel")]
 KEY = ["UTCHMMA", "UTCBAR", "LDTM", "STTM", "UBLKCP", "UTMALDG", "HMMA", "MOVM", "MUFU.TANH", "MUFU", "SYNCS", "BAR.SYNC", "FFMA", "DFMA", "DMUL", "DADD", "SHFL", "LDS", "STS"]
 
 sass = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True).stdout
