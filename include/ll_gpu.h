@@ -311,6 +311,22 @@ int ll_tc05_probe(int32_t device, const int32_t* args, float* d_out, double* res
 /* HBM copy bandwidth (read+write bytes / time), GB/s */
 int ll_microbench_copy(int32_t device, uint64_t bytes, int32_t iters, double* gbps);
 
+/* ---- allocation-free top-k (no counterpart in the reference) -------------
+ * For callers that may not call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it):
+ * the radix select of ll_local_topk / ll_select over the caller's own DEVICE array d_fitness[n], enqueued on `cuda_stream`
+ * (NULL = the default stream) of `device` (< 0 = the current one), returning immediately.  d_out[0..k) (DEVICE memory) receives
+ * the k smallest (fitness, first_global + position) pairs in ascending (fitness, index) order, bit-identical to ll_local_topk on
+ * the same values.  It calls no cudaMalloc / cudaFree / allocating library routine: its scratch (select state, candidates, one
+ * 64-bit key per member) is a file-scope device array of LL_TOPK_STATIC_SCRATCH_BYTES that every GPU which loads the library
+ * holds until the process exits.  Limits: 1 <= n <= LL_TOPK_STATIC_MAX, 1 <= k <= min(n, 4096); anything larger is rejected with
+ * LL_EINVAL and a message naming the limit.  All calls on one GPU share the array (it keeps the last call's contents; the state
+ * that must start at zero is rewritten by the first kernel of every call), so calls that overlap on one GPU — different
+ * streams, or different threads — race: serialise them. */
+#define LL_TOPK_STATIC_MAX (1u << 20)
+#define LL_TOPK_STATIC_SCRATCH_BYTES (2048u + 4096u * 16u + 8u * LL_TOPK_STATIC_MAX) /* 8.07 MB per GPU */
+int ll_topk_static(int32_t device, void* cuda_stream, const double* d_fitness, uint64_t n, uint64_t first_global, uint32_t k,
+                   ll_cand* d_out);
+
 #ifdef __cplusplus
 }
 #endif

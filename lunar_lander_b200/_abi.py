@@ -136,6 +136,7 @@ SIGNATURES = {
     "ll_step_counter": (C.c_int, [_ctx, _f64p, _u64p, C.c_int]),
     "ll_microbench_fma": (C.c_int, [C.c_int32, C.c_int32, C.c_double, _f64p, _f64p]),
     "ll_microbench_copy": (C.c_int, [C.c_int32, C.c_uint64, C.c_int32, _f64p]),
+    "ll_topk_static": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_void_p]),
     "ll_tc05_probe": (C.c_int, [C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_float), _f64p]),
 }
 

@@ -12,6 +12,8 @@
 // Random numbers are Philox4x32-10 counters keyed by (seed, generation, GLOBAL member, canonical parameter pair)
 // (ll_philox.h), so children do not depend on the GPU count, the shard or the launch geometry.
 // All of these kernels are HBM-bound streaming kernels: coalesced row reads/writes, one pass each.
+#include <mutex>
+
 #include "ll_ops.cuh"
 #include "ll_philox.h"
 
@@ -436,4 +438,99 @@ int ll_launch_gather(ll_ctx* ctx, const unsigned long long* d_idx, unsigned int 
                                                                     ctx->pop_local, ctx->topo.p_dev, static_cast<float*>(d_out), zero_unowned);
     LL_CUDA(ctx, cudaGetLastError());
     return LL_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------- K2 without allocations
+// ll_topk_static: the same radix select as ll_launch_topk over a caller's DEVICE fitness array, for callers that may not allocate
+// (CUDA graph capture, tight serving loops).  No counterpart in the reference.
+// The scratch (select state, candidate list, orderable keys) lives in ONE file-scope device array: every GPU that loads the library
+// holds LL_TOPK_STATIC_SCRATCH bytes until the process exits, every call on a device shares them, and the array keeps the last
+// call's contents — ll_keys_kernel rewrites the select state (prefix, k, ticket, candidate count, histogram) at the start of every
+// call and the keys are overwritten for [0, n), which is all the later kernels read.  Calls that overlap on one GPU race.
+namespace
+{
+    constexpr size_t TS_STATE_OFF = 0;                                        // ll_select_state (1048 bytes)
+    constexpr size_t TS_CAND_OFF  = 2048;                                     // ll_cand[LL_MAX_TOP]
+    constexpr size_t TS_KEYS_OFF  = TS_CAND_OFF + sizeof(ll_cand) * LL_MAX_TOP; // u64[LL_TOPK_STATIC_MAX]
+    constexpr size_t TS_BYTES     = TS_KEYS_OFF + sizeof(unsigned long long) * (size_t)LL_TOPK_STATIC_MAX;
+    static_assert(sizeof(ll_select_state) <= TS_CAND_OFF && TS_KEYS_OFF % 256 == 0 && TS_BYTES == LL_TOPK_STATIC_SCRATCH_BYTES, "scratch layout");
+
+    static __device__ __align__(256) unsigned char ll_topk_static_scratch[TS_BYTES];
+
+    struct ts_device
+    {
+        unsigned char* scratch = nullptr; // DEVICE address of ll_topk_static_scratch on this GPU (the name itself is a host-side stand-in)
+        int sm_count           = 0;
+    };
+    constexpr int TS_MAX_DEVICES = 64;
+    ts_device g_ts[TS_MAX_DEVICES];
+    std::mutex g_ts_mutex;
+
+    // once per device, with that device current
+    int ts_setup(int device, ts_device* out)
+    {
+        std::lock_guard<std::mutex> lock(g_ts_mutex);
+        ts_device& d = g_ts[device];
+        if (!d.scratch)
+        {
+            void* p = nullptr;
+            LL_CUDA(nullptr, cudaGetSymbolAddress(&p, ll_topk_static_scratch));
+            int sms = 0;
+            LL_CUDA(nullptr, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+            int smem_max = 0;
+            LL_CUDA(nullptr, cudaDeviceGetAttribute(&smem_max, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+            if ((size_t)smem_max < (size_t)LL_MAX_TOP * 16) return ll_fail(nullptr, LL_ENODEVICE, "ll_topk_static: too little shared memory per block");
+            d.sm_count = sms, d.scratch = static_cast<unsigned char*>(p);
+        }
+        *out = d;
+        return LL_OK;
+    }
+
+    int ts_run(int device, cudaStream_t stream, const double* d_fitness, unsigned long long n, unsigned long long first_global, unsigned int k,
+               ll_cand* d_out)
+    {
+        ts_device dev;
+        if (const int rc = ts_setup(device, &dev)) return rc;
+        ll_select_state* st      = reinterpret_cast<ll_select_state*>(dev.scratch + TS_STATE_OFF);
+        ll_cand* cand            = reinterpret_cast<ll_cand*>(dev.scratch + TS_CAND_OFF);
+        unsigned long long* keys = reinterpret_cast<unsigned long long*>(dev.scratch + TS_KEYS_OFF);
+        const unsigned int blocks = (unsigned int)((n + 255) / 256);
+        ll_keys_kernel<<<blocks, 256, 0, stream>>>(d_fitness, n, keys, st, k);
+        const unsigned int hb = blocks < (unsigned int)(dev.sm_count * 8) ? blocks : (unsigned int)(dev.sm_count * 8);
+        for (int pass = 0; pass < 12; ++pass) ll_select_hist_kernel<<<hb, 256, 0, stream>>>(keys, n, pass, st);
+        ll_select_collect_kernel<<<blocks, 256, 0, stream>>>(keys, n, first_global, st, cand, LL_MAX_TOP);
+        unsigned int np2 = 2;
+        while (np2 < k) np2 <<= 1;
+        // per call, not at set-up: ll_launch_topk sets this attribute of the same kernel to its own (possibly smaller) size
+        LL_CUDA(nullptr, cudaFuncSetAttribute(ll_select_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(np2 * 16)));
+        ll_select_sort_kernel<<<1, np2 / 2 < 1024 ? (np2 / 2 < 32 ? 32 : np2 / 2) : 1024, (size_t)np2 * 16, stream>>>(cand, k, np2);
+        LL_CUDA(nullptr, cudaGetLastError());
+        LL_CUDA(nullptr, cudaMemcpyAsync(d_out, cand, sizeof(ll_cand) * k, cudaMemcpyDeviceToDevice, stream));
+        return LL_OK;
+    }
+} // namespace
+
+extern "C" int ll_topk_static(int32_t device, void* cuda_stream, const double* d_fitness, uint64_t n, uint64_t first_global, uint32_t k,
+                              ll_cand* d_out)
+{
+    if (!d_fitness || !d_out) return ll_fail(nullptr, LL_EINVAL, "ll_topk_static: null argument");
+    if (n == 0 || n > LL_TOPK_STATIC_MAX)
+        return ll_fail(nullptr, LL_EINVAL,
+                       "ll_topk_static: n = " + std::to_string(n) + " is outside 1.." + std::to_string((unsigned long long)LL_TOPK_STATIC_MAX) +
+                           " (LL_TOPK_STATIC_MAX, the size of the static scratch array); use ll_local_topk on a context for larger shards");
+    if (k == 0 || k > n || k > LL_MAX_TOP)
+        return ll_fail(nullptr, LL_EINVAL, "ll_topk_static: k = " + std::to_string(k) + " is outside 1..min(n, " + std::to_string(LL_MAX_TOP) + ")");
+    int n_dev = 0, prev = -1;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0)
+    {
+        cudaGetLastError();
+        return ll_fail(nullptr, LL_ENODEVICE, "ll_topk_static: no CUDA device");
+    }
+    LL_CUDA(nullptr, cudaGetDevice(&prev));
+    if (device < 0) device = prev;
+    if (device >= n_dev || device >= TS_MAX_DEVICES) return ll_fail(nullptr, LL_EINVAL, "ll_topk_static: no such device");
+    if (device != prev) LL_CUDA(nullptr, cudaSetDevice(device));
+    const int rc = ts_run(device, static_cast<cudaStream_t>(cuda_stream), d_fitness, n, first_global, k, d_out);
+    if (device != prev) cudaSetDevice(prev);
+    return rc;
 }
