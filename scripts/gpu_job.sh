@@ -13,6 +13,6 @@ case "$what" in
   bench)    timeout 900 python bench.py "$@" > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "rc=$?"; tail -3 gpurun_out/bench.err ;;
   ab)       scripts/bench_kernels.sh "$@" ;;
   launches) "$@" > gpurun_out/plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/launches.csv "$@" > gpurun_out/ncu.log 2>&1; tail -2 gpurun_out/plain.log ;;
-  ncu)      re=$1; shift; "$@" > gpurun_out/plain.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:"$re" -c 2 -o gpurun_out/prof "$@" > gpurun_out/ncu.log 2>&1; tail -2 gpurun_out/ncu.log ;;
+  ncu)      re=$1; shift; "$@" > gpurun_out/plain.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:"$re" -c ${NCU_COUNT:-2} -o gpurun_out/${NCU_OUT:-prof} "$@" > gpurun_out/ncu.log 2>&1; tail -2 gpurun_out/ncu.log ;;
   *) echo "unknown job $what"; exit 2 ;;
 esac
