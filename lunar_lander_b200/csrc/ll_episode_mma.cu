@@ -454,9 +454,11 @@ namespace
             int steps = 0, layout = 0;
             double acc  = 0.0;
             bool active = false;
+            const ll_resume_rec* recs = ra.r.rec + member * (size_t)ra.r.stride;
+            int next_rec              = cnt < 16 ? cnt : 16; // records beyond the 16 rows wait their turn (hand-over thresholds above 16)
             if (slot < cnt)
             {
-                const ll_resume_rec r = ra.r.rec[member * LL_RESUME_SLOTS + slot];
+                const ll_resume_rec r = recs[slot];
                 layout                = r.layout;
                 const ll_layout<float> lay = a.layouts[layout];
                 cx = lay.center_x, lpad = lay.lpad_x1, lpad_r = lay.lpad_right;
@@ -496,14 +498,19 @@ namespace
                 }
                 const unsigned pk = __shfl_sync(0xffffffffu, packed, 4 * (slot & 7));
                 const int action  = (pk >> (4 * (slot >> 3))) & 15;
+                bool done = false, landed = false, success = false;
+                float dist = 0.f;
                 if (active)
                 {
-                    bool landed = false, success = false;
-                    float dist  = 0.f;
                     const float sp = ll_env_step<float, LL_MODE_FAST>(env, p, action, steps == 0, cx, lpad, lpad_r, &landed, &success, &dist);
                     acc += (double)sp;
                     ++steps;
-                    if (landed || steps >= a.max_steps)
+                    done = landed || steps >= a.max_steps;
+                }
+                const unsigned fin = __ballot_sync(0xffffffffu, done && owner) & 0xffffu;
+                if (fin)
+                {
+                    if (done)
                     {
                         const float term = ll_terminal_penalty<float, LL_MODE_FAST>(env, p, steps, landed, success, dist);
                         if (owner)
@@ -511,8 +518,19 @@ namespace
                             a.ep_steps[member * (size_t)LT + layout] = steps | (landed ? (1 << 28) : 0) | ((landed && !success) ? (1 << 29) : 0) | (success ? (1 << 30) : 0);
                             a.ep_fit[member * (size_t)LT + layout]   = (double)term + acc;
                         }
-                        active = false;
+                        const int nr = next_rec + __popc(fin & ((1u << slot) - 1u));
+                        if (nr < cnt)
+                        { // the row takes the member's next waiting episode
+                            const ll_resume_rec r = recs[nr];
+                            layout                = r.layout;
+                            const ll_layout<float> lay = a.layouts[layout];
+                            cx = lay.center_x, lpad = lay.lpad_x1, lpad_r = lay.lpad_right;
+                            p     = ll_lander<float>{r.x, r.y, r.vx, r.vy, r.fuel};
+                            steps = r.steps, acc = r.acc;
+                        }
+                        else active = false;
                     }
+                    next_rec += __popc(fin);
                 }
             }
             __syncwarp();

@@ -186,10 +186,12 @@ struct ll_resume_rec
     int layout, steps, pad_;
     double acc;
 };
-#define LL_RESUME_SLOTS 16
+#define LL_RESUME_SLOTS 16 /* rows of the straggler kernel's tile */
+#define LL_RESUME_MAX 64   /* most episodes a member can hand over (they refill the 16 rows as episodes end) */
 struct ll_resume_args
 {
-    ll_resume_rec* rec;            // [n_members][LL_RESUME_SLOTS]
+    ll_resume_rec* rec;            // [n_members][stride]
+    int stride;                    // records per member (= the hand-over threshold)
     unsigned int* count;           // [n_members] records of the member (0: nothing handed over)
     unsigned int* list;            // members with records, in arrival order
     unsigned int* n;               // number of entries of `list`

@@ -627,9 +627,17 @@ def test_fast_tcgen05_kernel_tracks_exact_fp32(ll, po, topo, n_layouts, pop, mon
     got = {}
     # tc05 = tile kernel + hand-over of a member's last <= 16 running episodes to the 16-row mma.sync kernel (the default);
     # tc05_nocut = the tile kernel alone (LL_TC05_CUT=0)
-    for tag, kern, cut in (("tc05", "tc05", "16"), ("tc05", "tc05", "16"), ("tc05_nocut", "tc05", "0"), ("mma", "mma", "16")):
+    # tc05_s0/1/2 = LL_TC05_SPLIT variants (how a 128-wide layer's instructions are overlapped with its own epilogue): same products in
+    # the same order, so bit-identical results
+    for tag, kern, cut, split in (("tc05", "tc05", "16", None), ("tc05", "tc05", "16", None), ("tc05_nocut", "tc05", "0", None), ("mma", "mma", "16", None),
+                                  ("tc05_s0", "tc05", "16", "0"), ("tc05_s1", "tc05", "16", "1"), ("tc05_s2", "tc05", "16", "2"),
+                                  ("tc05_cut40", "tc05", "40", None), ("tc05_cut5", "tc05", "5", None)):
         monkeypatch.setenv("LL_FAST_KERNEL", kern)
         monkeypatch.setenv("LL_TC05_CUT", cut)
+        if split is None:
+            monkeypatch.delenv("LL_TC05_SPLIT", raising=False)
+        else:
+            monkeypatch.setenv("LL_TC05_SPLIT", split)
         eng, cfg = _engine(ll, sizes, pop, 32, mode=1)
         eng.set_members(0, members)
         fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
@@ -643,7 +651,10 @@ def test_fast_tcgen05_kernel_tracks_exact_fp32(ll, po, topo, n_layouts, pop, mon
             assert np.array_equal(got[tag][2], fit) and np.array_equal(got[tag][0], ep_steps)  # deterministic
         got[tag] = (ep_steps, flags, fit, lr)
         eng.close()
-    assert np.mean(got["tc05"][0] == got["tc05_nocut"][0]) >= 0.98
+    for v in ("tc05", "tc05_cut40", "tc05_cut5"):  # hand-over thresholds above 16 refill the straggler kernel's 16 rows
+        assert np.mean(got[v][0] == got["tc05_nocut"][0]) >= 0.98, v
+    for v in ("tc05_s0", "tc05_s1", "tc05_s2"):
+        assert np.array_equal(got[v][0], got["tc05"][0]) and np.array_equal(got[v][2], got["tc05"][2]), v
     want = po.evaluate(cfg.env_cfg(), sizes, 1, members.astype(np.float32), spad, lpad, d, 5000, 32, threads=8)
     ep_steps, flags, fit, lr = got["tc05"]
     assert np.mean(ep_steps == want["ep_steps"]) >= 0.95
