@@ -476,7 +476,8 @@ def measure(ctx, workload, steps, warmup, min_timed_s=1.5, e2e_steps=None, cpu_s
                              "peak": hmma_peak, "unit": "TFLOP/s"} if "_mma" in kernel else None),
             "roofline_ga": {"bound": "hbm", "achieved": ga_gbs, "peak": hbm_peak, "unit": "GB/s",
                             "frac": ga_gbs / hbm_peak if hbm_peak else None, "traffic": ncu_traffic("k4_" + topo, eng.pop_local - top),
-                            "kernel": "ll_create_population_kernel",
+                            "kernel": ("ll_create_population_f32_kernel<fast: Philox4x32-7 + SFU Box-Muller>" if mode == 1 and precision == 32 else
+                                       "ll_create_population_f32_kernel<host-reproducible normals>" if precision == 32 else "ll_create_population_kernel<double>"),
                             "kernel_ms_per_launch": kt.mutate_ms / max(1, kt.mutate_launches), "peak_source": hbm_src},
             "kernel_ms": {"episode": kt.episode_ms, "select": kt.select_ms, "gather": kt.gather_ms, "breed": kt.mutate_ms,
                           "wall_s_timed_region": t_wall},

@@ -81,7 +81,8 @@ namespace
     // float populations: one block per member row, ONE THREAD = 4 consecutive device-order parameters = one Philox block, four
     // Box-Muller variates in float (ll_normal4_f32), the parent's float4 (L2-resident), one 16-byte store.  No shared-memory staging,
     // no fp64: the kernel is bound by the HBM write of the children instead of the ALU (the fp64 polar transform above: 10 % of HBM).
-    __global__ void __launch_bounds__(256) ll_create_population_f32_kernel(const __grid_constant__ pop_args a)
+    // FAST (LL_MODE_FAST): the normals come from the special-function unit (ll_normal4_f32_fast) instead of the host-reproducible routine.
+    template <bool FAST> __global__ void __launch_bounds__(256) ll_create_population_f32_kernel(const __grid_constant__ pop_args a)
     {
         using O = exact_ops<float>;
         __shared__ int s_inject, s_parent;
@@ -110,7 +111,8 @@ namespace
             for (int qd = threadIdx.x; qd < qpr; qd += blockDim.x)
             {
                 float g[4];
-                ll_normal4_f32(a.seed, a.gen, (uint32_t)mg, (uint32_t)qd, g);
+                if constexpr (FAST) ll_normal4_f32_fast(a.seed, a.gen, (uint32_t)mg, (uint32_t)qd, g);
+                else ll_normal4_f32(a.seed, a.gen, (uint32_t)mg, (uint32_t)qd, g);
                 const int4 c = d2c4[qd];
                 float4 v;
                 if (inject) v = make_float4(O::mul(s_init, g[0]), O::mul(s_init, g[1]), O::mul(s_init, g[2]), O::mul(s_init, g[3]));
@@ -390,7 +392,8 @@ int ll_launch_create_population_gen(ll_ctx* ctx, int elitism, uint64_t gen)
     }
     else
     {
-        ll_create_population_f32_kernel<<<grid, 256, 0, ctx->stream>>>(a);
+        if (ctx->mode == LL_MODE_FAST) ll_create_population_f32_kernel<true><<<grid, 256, 0, ctx->stream>>>(a);
+        else ll_create_population_f32_kernel<false><<<grid, 256, 0, ctx->stream>>>(a);
     }
     LL_CUDA(ctx, cudaGetLastError());
     return LL_OK;

@@ -229,6 +229,56 @@ def test_create_population_bit_exact(ll, po, precision):
     eng.close()
 
 
+def test_fast_mode_children_are_gaussian_deterministic_and_shard_independent(ll):
+    """LL_MODE_FAST breeds float populations with normals from the special-function unit (ll_normal4_f32_fast: Philox4x32-7 +
+    lg2/sqrt/sin/cos.approx) — not reproducible on the host, so judged the way fast mode is: distribution (moments, Kolmogorov-Smirnov
+    against N(0,1), no correlation between neighbours), structure (elites kept, injected slots N(0, sigma_init^2), children = ONE elite
+    + N(0, sigma_mut^2)), run-to-run determinism, and independence of the shard count (the draw is keyed by global member and
+    device-order position)."""
+    from scipy import stats
+    sizes = util.TOPOLOGIES["16_64_32"]
+    pop, top = 4000, 10
+
+    def breed(rank=0, world=1):
+        eng, _ = _engine(ll, sizes, pop, 32, mode=1, top=top, seed=5247, rank=rank, world=world)
+        eng.set_population_strategy(2, 0.35)
+        eng.create_population(True)  # first population: N(0, 1) everywhere
+        return eng, eng.get_members(int(eng.info.first_global), int(eng.info.pop_local)).astype(np.float64)  # member indices are global
+
+    eng, g0 = breed()
+    z = g0.ravel()
+    assert abs(z.mean()) < 3e-3 and abs(z.std() - 1.0) < 3e-3
+    assert abs(stats.skew(z[:2_000_000])) < 0.01 and abs(stats.kurtosis(z[:2_000_000])) < 0.02
+    assert stats.kstest(z[:200_000], "norm").pvalue > 1e-3
+    assert abs(np.corrcoef(z[:-1], z[1:])[0, 1]) < 3e-3 and np.abs(z).max() < 5.9
+    # second generation: elites (rows 0..top-1, well separated) kept, injected slots fresh N(0,1), the others one elite + N(0, 0.1^2)
+    eng.set_members(0, np.linspace(-1.0, 1.0, eng.P, dtype=np.float32)[None, :] * np.arange(1, top + 1, dtype=np.float32)[:, None])
+    eng.mark_elites()
+    eng.set_epochs(3)
+    eng.create_population(True)
+    g1 = eng.get_members(0, pop).astype(np.float64)
+    elites = g1[:top]
+    inj = util.injected_mask(pop, top, 0.35)
+    assert abs(g1[inj].std() - 1.0) < 0.01
+    kids = g1[~inj][top:]
+    d = np.abs(kids[:, None, :64] - elites[None, :, :64]).mean(axis=2)  # distance to every elite over 64 parameters
+    parent = d.argmin(axis=1)
+    noise = (kids - elites[parent]) / 0.1
+    assert abs(noise.std() - 1.0) < 0.01 and abs(noise.mean()) < 0.01
+    assert len(np.unique(parent)) == top  # every elite is somebody's parent
+    eng.close()
+    # determinism and shard independence
+    eng2, h0 = breed()
+    assert np.array_equal(h0, g0)
+    eng2.close()
+    parts = []
+    for r in range(2):
+        sh, f = breed(r, 2)
+        parts.append(f)
+        sh.close()
+    assert np.array_equal(np.concatenate(parts), g0)
+
+
 def test_topk_with_ties_and_select(ll, po):
     sizes = util.TOPOLOGIES["8_16_8"]
     pop, top = 5000, 37
