@@ -17,7 +17,7 @@ try:
     d = json.loads(open(sys.argv[1]).read().strip().splitlines()[-1])
     print("  value %.4e e2e %.4e ms/step %.1f gen/s %.3f scaling %s K1 ms by rank %s invariance %s" % (
         d["value"], d["e2e"]["value"], d["ms_per_step"], d["generations_per_sec"], d["scaling"],
-        [round(x, 1) for x in d["roofline"]["kernel_ms_per_launch_by_rank"]], d.get("invariance", {}).get("sha256", "")[:16]))
+        [round(x, 1) for x in d["roofline"]["kernel_ms_per_launch_by_rank"]], ((d.get("invariance") or {}).get("sha256") or "")[:16]))
 except Exception as e:
     print("  no result:", e)
 PY
