@@ -478,7 +478,8 @@ def measure(ctx, workload, steps, warmup, min_timed_s=1.5, e2e_steps=None, cpu_s
                             "frac": ga_gbs / hbm_peak if hbm_peak else None, "traffic": ncu_traffic("k4_" + topo, eng.pop_local - top),
                             "kernel": ("ll_create_population_f32_kernel<fast: Philox4x32-7 + SFU Box-Muller>" if mode == 1 and precision == 32 else
                                        "ll_create_population_f32_kernel<host-reproducible normals>" if precision == 32 else "ll_create_population_kernel<double>"),
-                            "kernel_ms_per_launch": kt.mutate_ms / max(1, kt.mutate_launches), "peak_source": hbm_src},
+                            "kernel_ms_per_launch": kt.mutate_ms / max(1, steps), "launches_per_generation": kt.mutate_launches / max(1, steps),
+                            "peak_source": hbm_src},
             "kernel_ms": {"episode": kt.episode_ms, "select": kt.select_ms, "gather": kt.gather_ms, "breed": kt.mutate_ms,
                           "wall_s_timed_region": t_wall},
             "e2e": {"value": e2e_lander_steps / e2e_sec if e2e_sec > 0 else 0.0, "unit": "lander-steps/s",

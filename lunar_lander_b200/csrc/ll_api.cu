@@ -163,7 +163,7 @@ extern "C" void ll_destroy(ll_ctx* ctx)
     ll_comm_release(ctx);
     void* ptrs[] = {ctx->d_params, ctx->d_elites,   ctx->d_dev2canon, ctx->d_layouts, ctx->d_fitness, ctx->d_lr,        ctx->d_steps,
                     ctx->d_ep_steps, ctx->d_ep_fit, ctx->d_queue,     ctx->d_stats,   ctx->d_partials, ctx->d_sel,      ctx->d_keys,
-                    ctx->d_cand,   ctx->d_elite_idx, ctx->d_trace,    ctx->d_scratch, ctx->d_sim, ctx->d_part, ctx->d_resume};
+                    ctx->d_cand,   ctx->d_elite_idx, ctx->d_trace,    ctx->d_scratch, ctx->d_sim, ctx->d_part, ctx->d_resume, ctx->d_breed};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (ctx->h_pin) cudaFreeHost(ctx->h_pin);
@@ -249,6 +249,7 @@ extern "C" int ll_create(ll_ctx** out, const ll_env_cfg* env, const ll_net_cfg* 
     LL_CUDA_B(cudaMalloc(&ctx->d_elites, row * ctx->top));
     LL_CUDA_B(cudaMemsetAsync(ctx->d_elites, 0, row * ctx->top, ctx->stream));
     LL_CUDA_B(cudaMalloc(&ctx->d_dev2canon, sizeof(int) * d2c.size()));
+    LL_CUDA_B(cudaMalloc(&ctx->d_breed, sizeof(unsigned int) * ctx->pop_local));
     LL_CUDA_B(cudaMemcpy(ctx->d_dev2canon, d2c.data(), sizeof(int) * d2c.size(), cudaMemcpyHostToDevice));
     LL_CUDA_B(cudaMalloc(&ctx->d_fitness, sizeof(double) * ctx->pop_local));
     LL_CUDA_B(cudaMalloc(&ctx->d_lr, sizeof(double) * ctx->pop_local));
@@ -324,7 +325,7 @@ int ll_launch_create_population_gen(ll_ctx* ctx, int elitism, uint64_t gen);
 extern "C" int ll_create_population(ll_ctx* ctx, int elitism)
 {
     LL_CHECK_CTX(ctx);
-    scope s(ctx, CLS_MUTATE, 1);
+    scope s(ctx, CLS_MUTATE, ctx->precision == 32 ? 2 : 1); // float: breeding decisions + the flat kernel
     LL_TRY(ll_launch_create_population_gen(ctx, elitism, ctx->has_elites ? ctx->epochs + 1 : ctx->epochs));
     ctx->have_results = false;
     return LL_OK;
@@ -591,7 +592,7 @@ extern "C" int ll_step_generation(ll_ctx* ctx, int32_t max_steps, int elitism, l
         LL_TRY(ll_comm_select(ctx, false));
     }
     {
-        scope s(ctx, CLS_MUTATE, 1);
+        scope s(ctx, CLS_MUTATE, ctx->precision == 32 ? 2 : 1); // float: breeding decisions + the flat kernel
         LL_TRY(ll_launch_create_population_gen(ctx, elitism, ctx->epochs + 1));
     }
     ctx->epochs += 1;
@@ -808,7 +809,7 @@ extern "C" int ll_deserialize(ll_ctx* ctx, const char* path)
     if (gen0 != ~0ull) ctx->seed = gen0 & 0xffffffffull; // the generator line carries the GA key of the run that wrote the file
     // the file holds the parent set only; slots [top, pop) are rebuilt exactly as the CreatePopulation that
     // preceded the save built them (generation key = stored epoch count)
-    scope sc(ctx, CLS_MUTATE, 1);
+    scope sc(ctx, CLS_MUTATE, ctx->precision == 32 ? 2 : 1);
     LL_TRY(ll_launch_create_population_gen(ctx, 1, e));
     ctx->have_results = false;
     return LL_OK;

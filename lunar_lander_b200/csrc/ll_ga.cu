@@ -12,6 +12,7 @@
 // Random numbers are Philox4x32-10 counters keyed by (seed, generation, GLOBAL member, canonical parameter pair)
 // (ll_philox.h), so children do not depend on the GPU count, the shard or the launch geometry.
 // All of these kernels are HBM-bound streaming kernels: coalesced row reads/writes, one pass each.
+#include <algorithm>
 #include <mutex>
 
 #include "ll_ops.cuh"
@@ -78,47 +79,64 @@ namespace
         }
     }
 
-    // float populations: one block per member row, ONE THREAD = 4 consecutive device-order parameters = one Philox block, four
-    // Box-Muller variates in float (ll_normal4_f32), the parent's float4 (L2-resident), one 16-byte store.  No shared-memory staging,
-    // no fp64: the kernel is bound by the HBM write of the children instead of the ALU (the fp64 polar transform above: 10 % of HBM).
+    // float populations, two launches:
+    //   ll_pop_meta_kernel: one thread per member decides how its row is bred — copy of elite r (elitism), fresh N(0, sigma_init^2)
+    //     individual, or child of ONE uniformly picked elite (ll_parent_pick: a Philox block of its own) — into a 4-byte word;
+    //   ll_create_population_f32_kernel: one WARP per member row (persistent warps stride over the rows).  ONE THREAD = 4 consecutive
+    //     device-order parameters = one Philox block = four Box-Muller variates in float, the parent's float4 (L2-resident), one 16-byte
+    //     store; a warp writes 512 contiguous bytes per iteration.  No shared memory and no barrier (a block per row needed two
+    //     __syncthreads per row to broadcast the parent — a quarter of the warp samples sat there — and left 4.5 % of the lanes idle in the
+    //     ragged last iteration of a 2 203-quad row on 256 threads; flattening (member, quad) over the grid instead cost 25 more
+    //     instructions of 64-bit index arithmetic per piece and was slower).
     // FAST (LL_MODE_FAST): the normals come from the special-function unit (ll_normal4_f32_fast) instead of the host-reproducible routine.
-    template <bool FAST> __global__ void __launch_bounds__(256) ll_create_population_f32_kernel(const __grid_constant__ pop_args a)
+    constexpr unsigned int BREED_COPY = 0x80000000u, BREED_FRESH = 0x40000000u; // low bits: elite slot (copy source / parent)
+
+    __global__ void __launch_bounds__(256) ll_pop_meta_kernel(const __grid_constant__ pop_args a, unsigned int* __restrict__ breed)
+    {
+        const unsigned long long ml = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+        if (ml >= a.pop_local) return;
+        const unsigned long long mg = a.first_global + ml;
+        unsigned int w;
+        if (a.from_elites && mg < a.first_child) w = BREED_COPY | (unsigned int)mg; // elitism: slot r keeps elite r unchanged
+        else if (!a.from_elites || ll_is_injected(mg - a.first_child, a.n_children, a.n_inject)) w = BREED_FRESH;
+        else w = ll_parent_pick(a.seed, a.gen, (uint32_t)mg, a.top);
+        breed[ml] = w;
+    }
+
+    template <bool FAST>
+    __global__ void __launch_bounds__(256) ll_create_population_f32_kernel(const __grid_constant__ pop_args a, const unsigned int* __restrict__ breed)
     {
         using O = exact_ops<float>;
-        __shared__ int s_inject, s_parent;
-        const int qpr = a.p_dev >> 2; // quads per row (p_dev is a multiple of 8)
-        const int4* d2c4 = reinterpret_cast<const int4*>(a.dev2canon);
+        const int qpr        = a.p_dev >> 2; // quads per row (p_dev is a multiple of 8)
+        const int4* d2c4     = reinterpret_cast<const int4*>(a.dev2canon);
+        const float4* elites = reinterpret_cast<const float4*>(a.elites);
         const float s_init = (float)a.sigma_init, s_mut = (float)a.sigma_mut;
-        for (unsigned long long ml = blockIdx.x; ml < a.pop_local; ml += gridDim.x)
+        const int lane = threadIdx.x & 31;
+        const unsigned long long n_warps = (unsigned long long)gridDim.x * (blockDim.x >> 5);
+        for (unsigned long long ml = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5; ml < a.pop_local; ml += n_warps)
         {
-            const unsigned long long mg = a.first_global + ml;
-            float4* row = reinterpret_cast<float4*>(static_cast<float*>(a.params) + ml * (size_t)a.p_dev);
-            if (a.from_elites && mg < a.first_child)
-            { // elitism: slot r keeps elite r unchanged
-                const float4* src = reinterpret_cast<const float4*>(static_cast<const float*>(a.elites) + mg * (size_t)a.p_dev);
-                for (int qd = threadIdx.x; qd < qpr; qd += blockDim.x) row[qd] = src[qd];
+            const unsigned int w = breed[ml];
+            const uint32_t mg    = (uint32_t)(a.first_global + ml);
+            float4* row          = reinterpret_cast<float4*>(static_cast<float*>(a.params) + ml * (size_t)a.p_dev);
+            const float4* src    = elites + (size_t)(w & 0x3fffffffu) * qpr; // copy source or parent (unused for fresh individuals)
+            if (w & BREED_COPY)
+            {
+                for (int qd = lane; qd < qpr; qd += 32) row[qd] = src[qd];
                 continue;
             }
-            if (threadIdx.x == 0)
-            {
-                const bool inject = !a.from_elites || ll_is_injected(mg - a.first_child, a.n_children, a.n_inject);
-                s_inject = inject ? 1 : 0;
-                s_parent = inject ? 0 : (int)ll_parent_pick(a.seed, a.gen, (uint32_t)mg, a.top);
-            }
-            __syncthreads();
-            const bool inject   = s_inject != 0;
-            const float4* parent = reinterpret_cast<const float4*>(static_cast<const float*>(a.elites) + (size_t)s_parent * a.p_dev);
-            for (int qd = threadIdx.x; qd < qpr; qd += blockDim.x)
+            const bool fresh = (w & BREED_FRESH) != 0u;
+#pragma unroll 2
+            for (int qd = lane; qd < qpr; qd += 32)
             {
                 float g[4];
-                if constexpr (FAST) ll_normal4_f32_fast(a.seed, a.gen, (uint32_t)mg, (uint32_t)qd, g);
-                else ll_normal4_f32(a.seed, a.gen, (uint32_t)mg, (uint32_t)qd, g);
+                if constexpr (FAST) ll_normal4_f32_fast(a.seed, a.gen, mg, (uint32_t)qd, g);
+                else ll_normal4_f32(a.seed, a.gen, mg, (uint32_t)qd, g);
                 const int4 c = d2c4[qd];
                 float4 v;
-                if (inject) v = make_float4(O::mul(s_init, g[0]), O::mul(s_init, g[1]), O::mul(s_init, g[2]), O::mul(s_init, g[3]));
+                if (fresh) v = make_float4(O::mul(s_init, g[0]), O::mul(s_init, g[1]), O::mul(s_init, g[2]), O::mul(s_init, g[3]));
                 else
                 {
-                    const float4 pr = parent[qd];
+                    const float4 pr = src[qd];
                     v = make_float4(O::add(pr.x, O::mul(s_mut, g[0])), O::add(pr.y, O::mul(s_mut, g[1])), O::add(pr.z, O::mul(s_mut, g[2])),
                                     O::add(pr.w, O::mul(s_mut, g[3])));
                 }
@@ -128,7 +146,6 @@ namespace
                 if (c.w < 0) v.w = 0.f;
                 row[qd] = v;
             }
-            __syncthreads();
         }
     }
 
@@ -392,8 +409,10 @@ int ll_launch_create_population_gen(ll_ctx* ctx, int elitism, uint64_t gen)
     }
     else
     {
-        if (ctx->mode == LL_MODE_FAST) ll_create_population_f32_kernel<true><<<grid, 256, 0, ctx->stream>>>(a);
-        else ll_create_population_f32_kernel<false><<<grid, 256, 0, ctx->stream>>>(a);
+        ll_pop_meta_kernel<<<(unsigned int)((ctx->pop_local + 255) / 256), 256, 0, ctx->stream>>>(a, ctx->d_breed);
+        const unsigned int blocks = (unsigned int)std::min<unsigned long long>((ctx->pop_local + 7) / 8, (unsigned long long)ctx->sm_count * 8);
+        if (ctx->mode == LL_MODE_FAST) ll_create_population_f32_kernel<true><<<blocks, 256, 0, ctx->stream>>>(a, ctx->d_breed);
+        else ll_create_population_f32_kernel<false><<<blocks, 256, 0, ctx->stream>>>(a, ctx->d_breed);
     }
     LL_CUDA(ctx, cudaGetLastError());
     return LL_OK;

@@ -90,6 +90,7 @@ struct ll_ctx
     void* d_params   = nullptr; // [pop_local][p_dev] T
     void* d_elites   = nullptr; // [top][p_dev] T
     int* d_dev2canon = nullptr; // [p_dev]
+    unsigned int* d_breed = nullptr; // [pop_local] per-member breeding decision of K4 (ll_pop_meta_kernel): elite copy / fresh / parent slot
     void* d_layouts  = nullptr; // [n_layouts] ll_layout<T>
     int n_layouts = 0, layouts_cap = 0;
     double *d_fitness = nullptr, *d_lr = nullptr, *d_steps = nullptr; // [pop_local]
