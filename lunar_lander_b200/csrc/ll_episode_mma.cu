@@ -276,7 +276,9 @@ namespace
             double acc = 0.0;
             bool active = false;
             double fit_sum = 0.0;
-            unsigned int steps_sum = 0, succ0 = 0, succ1 = 0;
+            unsigned long long steps_sum = 0; // 4096 layouts x 2^28 steps do not fit 32 bits
+            unsigned int succ0 = 0, succ1 = 0;
+            bool publish = true; // false for a chunk that is not the last of its member to arrive
             int next_layout = L < 16 ? L : 16;
             if (slot < L)
             {
@@ -343,7 +345,7 @@ namespace
                     {
                         const float term = ll_terminal_penalty<float, LL_MODE_FAST>(env, p, steps, landed, success, dist);
                         const double fit = (double)term + acc;
-                        fit_sum += fit, steps_sum += (unsigned)steps;
+                        fit_sum += fit, steps_sum += (unsigned long long)steps;
                         if (success) (dir == 0 ? succ0 : succ1) += 1u;
                         if (a.ep_steps && owner)
                         {
@@ -396,12 +398,12 @@ namespace
                         f = 0.0;
                         for (int l = 0; l < a.n_layouts; ++l) f += ef[l];
                     }
-                    fit_sum = f, steps_sum = (unsigned int)st, succ0 = (unsigned int)s0, succ1 = (unsigned int)s1;
+                    fit_sum = f, steps_sum = (unsigned long long)st, succ0 = (unsigned int)s0, succ1 = (unsigned int)s1;
                     a.part_count[member] = 0u;
                 }
-                else steps_sum = 0xffffffffu; // not the last: nothing to publish
+                else publish = false;
             }
-            if (lane == 0 && steps_sum != 0xffffffffu)
+            if (lane == 0 && publish)
             {
                 float bonus0 = 0.f, bonus1 = 0.f;
                 for (unsigned i = 0; i < succ0; ++i) bonus0 += env.tp_landed_lr_bonus;

@@ -161,11 +161,17 @@ int ll_file_read(const char* path, std::vector<uint64_t>* sizes, uint64_t* pop, 
     }
     for (char s : seen)
         if (!s) return bad("missing pop/layer block");
-    // "generator": 624 (libc++) or 625 (libstdc++) integers follow; only the first one is used (the Philox key)
+    // "generator": 624 (libc++) or 625 (libstdc++) integers follow.  Word 0 is the Philox key of the run that wrote the file IF the line
+    // starts like a freshly seeded std::mt19937 (word 1 = 1812433253 (w0 ^ w0 >> 30) + 1: what ll_file_write emits); a file written by
+    // the real ma-libs holds an arbitrary engine state there, which is not a seed: it is left alone and the configured seed stays.
     if (generator_word0)
     {
-        uint64_t w = 0;
-        if ((f >> tok) && tok == "generator" && (f >> w)) *generator_word0 = w;
+        uint64_t w0 = 0, w1 = 0;
+        if ((f >> tok) && tok == "generator" && (f >> w0) && (f >> w1))
+        {
+            const uint32_t s0 = static_cast<uint32_t>(w0);
+            if (static_cast<uint32_t>(w1) == 1812433253u * (s0 ^ (s0 >> 30)) + 1u) *generator_word0 = s0;
+        }
     }
     return LL_OK;
 }

@@ -209,12 +209,18 @@ namespace nn
             fwd_.assign(pop_ * P_, T(0));
             read_section(f, "vBiases_start", "vBiases_end", true);
             read_section(f, "vWeights_start", "vWeights_end", false);
-            // "generator": 624 (libc++) or 625 (libstdc++) integers; the first one keys the Philox GA (state word 0 of a
-            // freshly seeded mt19937 = its seed), the way the real Deserialize restores its mt19937 from this line.
+            // "generator": 624 (libc++) or 625 (libstdc++) integers.  A line that starts like a FRESHLY SEEDED mt19937 (word 1 follows
+            // from word 0 by the seeding recurrence — what this stand-in and libll_gpu write) carries the Philox key of the run that
+            // wrote the file in word 0, and the resumed run continues with it, the way the real Deserialize restores its mt19937.  Any
+            // other line (a file written by the real ma-libs: an arbitrary engine state) leaves the configured seed alone.
             {
                 std::string gtok;
-                unsigned long w0 = 0;
-                if ((f >> gtok) && gtok == "generator" && (f >> w0)) seed_ = static_cast<uint32_t>(w0);
+                unsigned long w0 = 0, w1 = 0;
+                if ((f >> gtok) && gtok == "generator" && (f >> w0) && (f >> w1))
+                {
+                    const uint32_t s0 = static_cast<uint32_t>(w0);
+                    if (static_cast<uint32_t>(w1) == 1812433253u * (s0 ^ (s0 >> 30)) + 1u) seed_ = s0;
+                }
             }
             for (size_t r = 0; r < top_; ++r) rebuild_forward(r);
             has_elites_ = true;

@@ -5,6 +5,13 @@ oracle/Makefile with the ma-libs stand-ins): same config.txt, same seeds ->
   * identical checkpoint files up to the `generator` line, identical file names,
   * identical behaviour of --continue (resume from <name>_last.txt) and of the unreachable --step file name.
 Reference interfaces: src/main_train.cpp:14-106, src/nn_engine_trainer.cpp:67-438.
+
+What this identity pins, and what it does not: both binaries link a stand-in for the un-vendored ma-libs (oracle/shim: config loader,
+thread pool, nn::ANN_MLP_GA<T>), and that stand-in includes the product's ll_math.h / ll_philox.h.  So the identity holds MODULO THE
+MA-LIBS SHIM: it pins the reference's host loop, environment, penalties, layout generation / balancing, logging and file naming
+(all compiled from the reference's own sources); the policy forward pass, the GA and the Serialize token format are this repo's
+restatement on both sides (parity unpinned at the ma-libs boundary; tests/test_oracle.py measures how the
+restated tanh flies the sample elites against libm's).
 """
 import os
 import re
