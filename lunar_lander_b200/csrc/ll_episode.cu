@@ -87,6 +87,15 @@ namespace
         }
     };
 
+    template <> struct vec_loader<float, 1>
+    {
+        static __device__ __forceinline__ void load(const float* p, float* v) { v[0] = p[0]; }
+    };
+    template <> struct vec_loader<double, 1>
+    {
+        static __device__ __forceinline__ void load(const double* p, double* v) { v[0] = p[0]; }
+    };
+
     // TILE consecutive output neurons of one layer for this lane's episode.
     //   w   : &Wt[0][o0] of the lane's member (shared memory), row pitch out_pad
     //   ain : this lane's activation column of the previous layer, element k at ain[k * P] (P: row pitch of the activation
@@ -121,7 +130,9 @@ namespace
     // Q > 1: the episode's column is shared by Q lanes (sub = 0..Q-1), each taking every Q-th tile of 4 output neurons; a neuron's
     // own arithmetic (sequential-k multiply-add, bias last, activation) is untouched, so the result is bit-identical to Q == 1.
     // Every lane of the warp must call this together when Q > 1 (warp barriers between layers).
-    template <typename T, int MODE>
+    // WIDE: compiled for Q >= 16 only (one neuron per lane) — its own instantiation so that the register tiles of the other paths do
+    // not set the kernel's register count (small populations want many resident warps).
+    template <typename T, int MODE, bool WIDE = false>
     __device__ __forceinline__ int forward(const ll_topo& tp, const T* __restrict__ wrow, T* a0, T* a1, int sub = 0, int Q = 1, int P = 32)
     {
         constexpr int BIG = sizeof(T) == 4 ? 16 : 8;
@@ -132,7 +143,12 @@ namespace
             const int in = tp.in[l], op = tp.out_pad[l];
             const T* w = wrow + tp.w_off[l];
             const T* b = wrow + tp.b_off[l];
-            if (Q > 1)
+            if constexpr (WIDE)
+            { // one neuron per lane (small populations: a whole half-warp or warp flies ONE episode, the layer's neurons side by side)
+                for (int o = sub; o < tp.out[l]; o += Q) layer_tile<T, MODE, 1>(w + o, b + o, ain, aout + o * P, in, op, tp.activation, P);
+                __syncwarp();
+            }
+            else if (Q > 1)
             {
                 for (int o = sub * 4; o < op; o += Q * 4) layer_tile<T, MODE, 4>(w + o, b + o, ain, aout + o * P, in, op, tp.activation, P);
                 __syncwarp();
@@ -198,9 +214,9 @@ namespace
 
     // RP: the activation buffers have a run-time row pitch (Q > 1 and wide layers, see the launcher); otherwise the pitch is the
     // constant 32 and a slot's column is its first lane, which keeps the address arithmetic of the inner loops in immediates.
-    template <typename T, int MODE, bool RP>
-    __global__ void __launch_bounds__(128) ll_episode_kernel(const __grid_constant__ ll_topo tp, const __grid_constant__ ll_env<T> env,
-                                                             const __grid_constant__ ep_dev_args a)
+    template <typename T, int MODE, bool RP, bool WIDE = false>
+    __global__ void __launch_bounds__(128, WIDE ? 6 : 1) ll_episode_kernel(const __grid_constant__ ll_topo tp, const __grid_constant__ ll_env<T> env,
+                                                                           const __grid_constant__ ep_dev_args a)
     {
         using O = ll_ops<T, MODE>;
         extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -274,7 +290,7 @@ namespace
             while (__any_sync(0xffffffffu, active))
             {
                 write_state<T, MODE>(env, x, y, vx, vy, fuel, cx, act0, P);
-                const int action = forward<T, MODE>(tp, wrow, act0, act1, sub, Q, P);
+                const int action = forward<T, MODE, WIDE>(tp, wrow, act0, act1, sub, Q, P);
                 if (active)
                 {
                     // apply_action: src/game_logic.cpp:156-183
@@ -456,13 +472,19 @@ namespace
             // small population (the reference's own scale): a generation lasts as long as one lane's chain of steps, each a few
             // thousand fp64 instructions of ONE warp - deal the neurons of a slot to up to 4 lanes (and its layouts to more warps,
             // below) while the GPU has warps to spare.  configs[0], 100 x 50: 46.5 / 31.9 / 25.4 / 26.6 ms for Q = 1 / 2 / 4 / 8.
+            // Smaller still (configs[0]: 100 x 50 = 5 000 episodes for 148 SMs): ONE neuron per lane, Q = 16 lanes per episode (its own
+            // instantiation at 76 registers, 24 warps per SM), when all the (member, layout pair) work items are resident at once:
+            // 25.4 -> 18.6 ms per generation (Q = 32: 20.8 - more work items than warp slots).
             if (Q == 1 && h.ep_steps && h.ep_fit)
-                for (int q = 4; q > 1; q >>= 1)
+                for (int q = 16; q > 1; q >>= 1)
                 {
+                    if (q == 8) continue; // 8 lanes x tiles of 4 neurons: measured no better than 4 (26.6 vs 25.4 ms)
                     int g = 0, n = 0;
                     const unsigned long long tiles = geometry(q, &g, &n);
                     const unsigned long long ch    = L > 32 / q ? (unsigned long long)((L + 32 / q - 1) / (32 / q)) : 1ull;
-                    if (q <= widest / 4 && tiles * ch <= (unsigned long long)ctx->sm_count * 8ull)
+                    unsigned long long warps_per_sm = 8;
+                    if (q == 16) warps_per_sm = std::min<unsigned long long>(24, ((size_t)200 << 10) / ((size_t)tp.p_dev * sizeof(T) + 4096));
+                    if ((q == 16 ? widest >= 16 : q <= widest / 4) && tiles * ch <= (unsigned long long)ctx->sm_count * warps_per_sm)
                     {
                         Q = q;
                         break;
@@ -472,7 +494,7 @@ namespace
             if (force && *force)
             {
                 const int f = atoi(force);
-                if (f == 1 || f == 2 || f == 4 || f == 8) Q = f;
+                if (f == 1 || f == 2 || f == 4 || f == 8 || ((f == 16 || f == 32) && h.ep_steps && h.ep_fit)) Q = f;
             }
         }
         a.Q = Q;
@@ -534,8 +556,9 @@ namespace
         a.act_pitch = 32;
         int widest_out = 4;
         for (int l = 0; l < tp.n_layers; ++l) widest_out = std::max(widest_out, tp.out_pad[l]);
-        const bool rp = Q > 1 && widest_out >= 32; // narrow networks store little: the constant pitch is faster there (16_16: 6 %)
-        if (rp)
+        const bool rp = (Q > 1 && widest_out >= 32) || Q >= 16; // narrow networks store little: the constant pitch is faster there (16_16: 6 %)
+        if (Q >= 16) a.act_pitch = 32 / Q; // neuron per lane: the lanes of a slot store consecutive rows, E = 1 or 2 columns
+        else if (rp)
         {
             const int E = 32 / Q, W = 128 / (int)sizeof(T);
             int P = E;
@@ -554,7 +577,7 @@ namespace
         int wpb = 4;
         while (wpb > 1 && wpb * a.warp_bytes > max_smem / 2) wpb >>= 1; // prefer >= 2 blocks per SM
         const size_t smem = (size_t)wpb * a.warp_bytes;
-        auto kern         = rp ? ll_episode_kernel<T, MODE, true> : ll_episode_kernel<T, MODE, false>;
+        auto kern         = Q >= 16 ? ll_episode_kernel<T, MODE, true, true> : (rp ? ll_episode_kernel<T, MODE, true> : ll_episode_kernel<T, MODE, false>);
         LL_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int per_sm = 0;
         LL_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, wpb * 32, smem));
@@ -615,6 +638,7 @@ static bool ll_use_warp(const ll_ctx* ctx, int n_layouts)
 
 int ll_launch_episode(ll_ctx* ctx, const ll_episode_args& a)
 {
+    if (ctx->mode == LL_MODE_EXACT && ll_exactw_applicable(ctx, a)) return ll_launch_episode_exactw(ctx, a); // small populations
     if (ctx->precision == 64) return launch_t<double, LL_MODE_EXACT>(ctx, a);
     if (ctx->mode == LL_MODE_FAST)
     { // the team kernel needs weight reuse across layouts; traces and tiny layout counts stay lane-per-episode
@@ -637,6 +661,13 @@ int ll_launch_feedforward(ll_ctx* ctx, const void* member_row, const void* d_sta
 
 const char* ll_episode_kernel_name(const ll_ctx* ctx, int n_layouts)
 {
+    if (ctx->mode == LL_MODE_EXACT && n_layouts > 0)
+    { // what ll_evaluate will pick (per-episode arrays present, no trace)
+        ll_episode_args probe{};
+        probe.n_layouts = n_layouts, probe.n_members = ctx->pop_local;
+        probe.ep_steps = ctx->d_ep_steps, probe.ep_fit = ctx->d_ep_fit;
+        if (ll_exactw_applicable(ctx, probe)) return ctx->precision == 64 ? "ll_episode_exactw_kernel<double> (warp per episode)" : "ll_episode_exactw_kernel<float> (warp per episode)";
+    }
     if (ctx->precision == 64) return "ll_episode_kernel<double,exact>";
     if (ctx->mode == LL_MODE_FAST && ll_use_warp(ctx, n_layouts)) return "ll_episode_warp_kernel (warp per member, FFMA + shuffles)";
     if (ctx->mode == LL_MODE_FAST && ll_use_tc05(ctx, n_layouts)) return "ll_episode_tc05_kernel (tcgen05+TMEM; stragglers: mma.sync)";

@@ -203,6 +203,8 @@ bool ll_tc05_applicable(const ll_ctx* ctx, int n_layouts);
 // default choice of the tcgen05 kernel: where it applies (17..64 layouts, the instantiated topologies) and the shard fills its 6 member
 // slots per SM; measured 1.18-1.25 x the mma.sync kernel on the benchmark workload together with the straggler hand-over
 #define LL_TC05_DEFAULT(ctx, n_layouts) ((ctx)->pop_local >= 6ull * (unsigned long long)(ctx)->sm_count)
+int ll_launch_episode_exactw(ll_ctx* ctx, const ll_episode_args& a); // ll_episode_exactw.cu: exact mode, one warp per episode (small populations)
+bool ll_exactw_applicable(const ll_ctx* ctx, const ll_episode_args& a);
 int ll_launch_episode_warp(ll_ctx* ctx, const ll_episode_args& a); // ll_episode_warp.cu
 bool ll_warp_applicable(const ll_ctx* ctx, int n_layouts);
 #define LL_WARP_MAX_LAYOUTS 1 /* default choice of the warp-per-member kernel: a single layout per member (configs[1]) */

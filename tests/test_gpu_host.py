@@ -94,7 +94,7 @@ def test_main_train_d_matches_reference_log_and_files(tmp_path, built):
     files = compare_runs(ours, ref, r_our, r_ref)
     assert "lunar_lander_last.txt" in files and "lunar_lander_5_16_16_4_s_0010.txt" in files
     assert "Stagnation detected" in r_ref[1], "the case is meant to cover a layout reset"
-    assert "ll_episode_kernel<double,exact>" in r_our[2]
+    assert "ll_episode_exactw_kernel<double>" in r_our[2]  # 100 x 50: the small-population exact kernel
 
 
 def test_continue_resumes_like_the_reference(tmp_path, built):

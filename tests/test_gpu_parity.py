@@ -97,7 +97,7 @@ def test_generation_bit_exact(ll, po, precision, n_layouts):
 
 
 @pytest.mark.parametrize("precision", [64, 32])
-@pytest.mark.parametrize("q", [1, 2, 4, 8])
+@pytest.mark.parametrize("q", [1, 2, 4, 8, 16, 32])
 @pytest.mark.parametrize("topo,n_layouts", [("8_16_32_16_8", 50), ("16_16", 5), ("32_128_32", 13)])
 def test_exact_kernel_lane_split_bit_exact(ll, po, precision, q, topo, n_layouts, monkeypatch):
     """LL_EXACT_Q lanes per episode slot (the slot's output neurons dealt to Q lanes; chosen automatically for small populations):
@@ -116,6 +116,43 @@ def test_exact_kernel_lane_split_bit_exact(ll, po, precision, q, topo, n_layouts
     assert np.array_equal(ep_fit, want["ep_fit"])
     assert np.array_equal(steps, want["steps"]) and np.array_equal(lr, want["lr"]) and np.array_equal(fit, want["fitness"])
     eng.close()
+
+
+@pytest.mark.parametrize("precision", [64, 32])
+@pytest.mark.parametrize("topo,n_layouts,pop", [("16_16", 50, 33), ("8_16_8", 1, 40), ("8_16_32_16_8", 7, 21), ("16_64_32", 8, 9), ("32_128_32", 13, 5),
+                                                ("16_32", 50, 3)])
+def test_exact_warp_per_episode_kernel_bit_exact(ll, po, precision, topo, n_layouts, pop, monkeypatch):
+    """ll_episode_exactw.cu (small populations, the reference's own scale: one warp = one episode, neurons across the lanes, topology
+    compiled in, weights from the read-only path, the member's last episode to finish sums its layouts in layout order): a neuron's
+    arithmetic is that of the tiled exact kernel, so per-episode and per-member results equal the oracle's bit for bit — forced on
+    (LL_EXACT_WARP=1), as the default choice for these sizes, and against the tiled kernel (LL_EXACT_WARP=0) on the same members."""
+    sizes = util.TOPOLOGIES[topo] if topo in util.TOPOLOGIES else [5] + [int(x) for x in topo.split("_")] + [4]
+    if topo in ("16_16", "8_16_8", "8_16_32_16_8", "16_64_32", "32_128_32"):
+        pe, sizes = util.elite_population(topo, max(2, pop // 2), 3)
+        members = np.concatenate([pe[:pop // 2], util.random_population(sizes, pop - pop // 2, 11)])
+    else:
+        members = util.random_population(sizes, pop, 11, scale=0.5)
+    spad, lpad, d = util.layouts(50)
+    spad, lpad, d = spad[:n_layouts], lpad[:n_layouts], d[:n_layouts]
+    got = {}
+    for force in ("1", None, "0"):
+        if force is None:
+            monkeypatch.delenv("LL_EXACT_WARP", raising=False)
+        else:
+            monkeypatch.setenv("LL_EXACT_WARP", force)
+        eng, cfg = _engine(ll, sizes, len(members), precision)
+        eng.set_members(0, members)
+        for _ in range(2):  # twice: the arrival counters are left at zero
+            fit, lr, steps, st = eng.evaluate(spad, lpad, d, 1500)
+        assert ("exactw" in eng.info.kernel.decode()) == (force != "0"), eng.info.kernel
+        got[force] = (fit, lr, steps) + eng.read_episodes()
+        assert st.sum_steps == steps.sum()
+        eng.close()
+    want = po.evaluate(cfg.env_cfg(), sizes, 1, members.astype(eng.dtype), spad, lpad, d, 1500, precision, threads=8)
+    for force, (fit, lr, steps, ep_steps, ep_flags, ep_fit) in got.items():
+        assert np.array_equal(ep_steps, want["ep_steps"]) and np.array_equal(ep_flags, want["ep_flags"]), force
+        assert np.array_equal(ep_fit, want["ep_fit"]), force
+        assert np.array_equal(steps, want["steps"]) and np.array_equal(lr, want["lr"]) and np.array_equal(fit, want["fitness"]), force
 
 
 @pytest.mark.parametrize("precision", [64, 32])
