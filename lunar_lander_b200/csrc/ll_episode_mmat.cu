@@ -215,13 +215,15 @@ namespace
     // Stage one member row (HBM layout of ll_topo: per layer Wt[k][out_pad] then b[out_pad]) into the A-fragment layout, splitting
     // every weight into its fp16 parts on the way.  Element (k, o): tile (o >> 4, k >> 4), row r = o & 15, column c = k & 15 ->
     // lane (r & 7) * 4 + ((c & 7) >> 1), word (r >> 3) + 2 * (c >> 3), half c & 1.
-    template <class N, int L> __device__ __forceinline__ void stage_t(const mmat_args& a, const float* __restrict__ row, float* __restrict__ sw, int lane)
+    // lane / nthreads: index and number of the threads that share the staging (a warp; the straggler pass: the two warps of a pair)
+    template <class N, int L>
+    __device__ __forceinline__ void stage_t(const mmat_args& a, const float* __restrict__ row, float* __restrict__ sw, int lane, int nthreads = 32)
     {
         constexpr int IN = N::sz(L), OUT = N::sz(L + 1), KT = N::k16(L) / 16, M16 = N::m16(L);
         const int op      = a.out_pad[L];
         const float4* src = reinterpret_cast<const float4*>(row + a.w_off[L]);
         __half* dst       = reinterpret_cast<__half*>(sw + N::w_off(L));
-        for (int i = lane; i < IN * op / 4; i += 32)
+        for (int i = lane; i < IN * op / 4; i += nthreads)
         {
             const float4 v = __ldg(src + i);
             const int k = (i * 4) / op, o0 = (i * 4) - k * op;
@@ -245,12 +247,12 @@ namespace
                 }
             }
         }
-        for (int i = lane; i < M16; i += 32)
+        for (int i = lane; i < M16; i += nthreads)
         { // word i of the bias block: tile i >> 4, g = (i >> 1) & 7, half i & 1 -> output 16mt + g + 8h
             const int o         = (i >> 4) * 16 + ((i >> 1) & 7) + 8 * (i & 1);
             sw[N::b_off(L) + i] = (o < OUT) ? __ldg(row + a.b_off[L] + o) : 0.f;
         }
-        if constexpr (L + 1 < N::NL) stage_t<N, L + 1>(a, row, sw, lane);
+        if constexpr (L + 1 < N::NL) stage_t<N, L + 1>(a, row, sw, lane, nthreads);
     }
 
     // warps per CTA (one CTA per SM): as many member rows as fit in 227 KB of shared memory, at most 16.  With one slot tile per warp
@@ -456,6 +458,153 @@ namespace
         }
     }
 
+    // ---- straggler pass behind the tcgen05 tile kernel (ll_episode_tc05.cu), slots on the N side: a member's handed-over episodes
+    // (lander state, step count, accumulated step penalty: ll_resume_rec) finish here.  TWO warps share one staged member: each flies an
+    // 8-column tile and both refill their columns from the member's waiting records (a shared-memory counter) as episodes end — the
+    // pass is a handful of long dependent chains per SM (shared memory holds 6 members of 32_128_32), so a second chain per member is
+    // worth more than the 45 % fewer HMMAs per step an 8-column tile costs against the 16-row M-side tile (ll_episode_mma.cu).  The
+    // pair then closes the member: every layout's result, the tile kernel's and ours, summed in layout order from the per-episode
+    // arrays (src/nn_engine_trainer.cpp:518-530).
+    struct mmat_resume_args
+    {
+        mmat_args m;
+        ll_resume_args r;
+    };
+    struct pair_ctl
+    {
+        unsigned int item;
+        int next_rec;
+    };
+
+    // member buffers per CTA of the straggler pass: what fits in shared memory, at most 6 (12 warps x <= 168 registers, barrier ids 1..6)
+    template <class N> __host__ __device__ constexpr int resume_pairs()
+    {
+        const int by_smem = (227 * 1024 - 256) / (N::total * 4);
+        return by_smem >= 6 ? 6 : (by_smem < 1 ? 1 : by_smem);
+    }
+    // WPM warps share one member (LL_TC05_RESUME_WARPS: 2 or 3)
+    template <int WPM> __device__ __forceinline__ void pair_sync(int pair) { asm volatile("bar.sync %0, %1;" : : "r"(1 + pair), "n"(32 * WPM) : "memory"); }
+
+    template <class N, int WPM>
+    __global__ void __launch_bounds__(32 * WPM * resume_pairs<N>(), 1) ll_episode_mmat_resume_kernel(const __grid_constant__ ll_env<float> env,
+                                                                                                const __grid_constant__ mmat_resume_args ra)
+    {
+        const mmat_args& a = ra.m;
+        extern __shared__ __align__(16) float smem_all[];
+        const int warp = threadIdx.x >> 5, pair = warp / WPM, half = warp % WPM; // half: which of the member's WPM tiles
+        float* sw      = smem_all + pair * N::total;
+        pair_ctl* ctl  = reinterpret_cast<pair_ctl*>(smem_all + resume_pairs<N>() * N::total) + pair;
+        const int lane   = threadIdx.x & 31;
+        const int g      = lane >> 2, t = lane & 3; // quad g holds column (slot) g, replicated in its four lanes
+        const bool owner = t == 0;
+        const int LT     = a.n_layouts;
+        for (int i = lane + 32 * half; i < N::total; i += 32 * WPM) sw[i] = 0.f;
+        const unsigned int n_items = *ra.r.n;
+        for (;;)
+        {
+            if (half == 0 && lane == 0) ctl->item = atomicAdd(a.queue, 1u);
+            pair_sync<WPM>(pair);
+            const unsigned int item = ctl->item;
+            if (item >= n_items) break;
+            const unsigned long long member = ra.r.list[item];
+            const int cnt                   = (int)ra.r.count[member];
+            const ll_resume_rec* recs       = ra.r.rec + member * (size_t)ra.r.stride;
+            stage_t<N, 0>(a, a.params + member * (size_t)a.p_dev, sw, lane + 32 * half, 32 * WPM);
+            if (half == 0 && lane == 0) ctl->next_rec = cnt < 8 * WPM ? cnt : 8 * WPM;
+            pair_sync<WPM>(pair);
+            ll_lander<float> p{0.f, 0.f, 0.f, 0.f, 0.f};
+            float cx = 0.f, lpad = 0.f, lpad_r = 0.f;
+            int steps = 0, layout = 0;
+            double acc  = 0.0;
+            bool active = false;
+            auto take = [&](int i) {
+                const ll_resume_rec r      = recs[i];
+                layout                     = r.layout;
+                const ll_layout<float> lay = a.layouts[layout];
+                cx = lay.center_x, lpad = lay.lpad_x1, lpad_r = lay.lpad_right;
+                p     = ll_lander<float>{r.x, r.y, r.vx, r.vy, r.fuel};
+                steps = r.steps, acc = r.acc;
+            };
+            if (8 * half + g < cnt)
+            {
+                take(8 * half + g);
+                active = true;
+            }
+            while (__ballot_sync(0xffffffffu, active) != 0u)
+            {
+                uint32_t xh[1][1][2], xl[1][1][2];
+                xh[0][0][1] = 0u, xl[0][0][1] = 0u;
+                {
+                    float st[5];
+                    ll_get_state<float, LL_MODE_FAST>(env, p, cx, st, 1);
+                    const float e0 = t == 0 ? st[0] : (t == 1 ? st[2] : (t == 2 ? st[4] : 0.f));
+                    const float e1 = t == 0 ? st[1] : (t == 1 ? st[3] : 0.f);
+                    split2(e0, e1, xh[0][0][0], xl[0][0][0]);
+                }
+                float z[1][2] = {{0.f, 0.f}};
+                tchain<N, 0, 1>::run(sw, lane, g, xh, xl, z);
+                unsigned packed = 0;
+#pragma unroll
+                for (int e = 0; e < 2; ++e)
+                { // argmax over outputs 0..3 of a slot (first maximum wins), as in the kernel above
+                    const float o0 = z[0][e];
+                    const float o1 = __shfl_xor_sync(0xffffffffu, o0, 4), o2 = __shfl_xor_sync(0xffffffffu, o0, 8);
+                    const float o3 = __shfl_xor_sync(0xffffffffu, o0, 12);
+                    float best = o0;
+                    unsigned idx = 0;
+                    if (o1 > best) best = o1, idx = 1;
+                    if (o2 > best) best = o2, idx = 2;
+                    if (o3 > best) best = o3, idx = 3;
+                    packed |= idx << (4 * e);
+                }
+                const unsigned pk = __shfl_sync(0xffffffffu, packed, g >> 1);
+                const int action  = (pk >> (4 * (g & 1))) & 15;
+                bool done = false, landed = false, success = false;
+                float dist = 0.f;
+                if (active)
+                {
+                    const float sp = ll_env_step<float, LL_MODE_FAST>(env, p, action, steps == 0, cx, lpad, lpad_r, &landed, &success, &dist);
+                    acc += (double)sp;
+                    ++steps;
+                    done = landed || steps >= a.max_steps;
+                }
+                const unsigned fin = __ballot_sync(0xffffffffu, done && owner); // bit 4g' = column g' ended
+                if (fin)
+                {
+                    int base = 0; // the pair's two tiles draw the waiting records from one counter
+                    if (lane == 0) base = atomicAdd(&ctl->next_rec, __popc(fin));
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (done)
+                    {
+                        const float term = ll_terminal_penalty<float, LL_MODE_FAST>(env, p, steps, landed, success, dist);
+                        if (owner)
+                        {
+                            a.ep_steps[member * (size_t)LT + layout] = steps | (landed ? (1 << 28) : 0) | ((landed && !success) ? (1 << 29) : 0) | (success ? (1 << 30) : 0);
+                            a.ep_fit[member * (size_t)LT + layout]   = (double)term + acc;
+                        }
+                        const int nr = base + __popc(fin & ((1u << (4 * g)) - 1u));
+                        if (nr < cnt) take(nr); // the column takes the member's next waiting episode
+                        else active = false;
+                    }
+                }
+            }
+            pair_sync<WPM>(pair); // both tiles are done, their results visible to the closing lane
+            if (half == 0 && lane == 0)
+            { // close the member: all layouts in layout order (the tile kernel wrote the others before this kernel started)
+                double f = 0.0, stp = 0.0;
+                float bonus0 = 0.f, bonus1 = 0.f;
+                for (int l = 0; l < LT; ++l)
+                {
+                    const int meta = a.ep_steps[member * (size_t)LT + l];
+                    f += a.ep_fit[member * (size_t)LT + l], stp += (double)(meta & 0x0fffffff);
+                    if (meta & (1 << 30)) (a.layouts[l].dir == 0 ? bonus0 : bonus1) += env.tp_landed_lr_bonus;
+                }
+                const double lr   = (double)(bonus1 < bonus0 ? bonus1 : bonus0);
+                a.fitness[member] = f - lr, a.lr[member] = lr, a.steps[member] = stp;
+            }
+        }
+    }
+
     int t_env_int(const char* name, int fallback)
     {
         const char* v = getenv(name);
@@ -511,6 +660,50 @@ namespace
         return true;
     }
 } // namespace
+
+#ifndef LL_TC05_RESUME_WARPS_DEFAULT
+#define LL_TC05_RESUME_WARPS_DEFAULT 2
+#endif
+namespace
+{
+    template <class N, int WPM> int launch_mmat_resume_t(ll_ctx* ctx, const ll_episode_args& h, const ll_resume_args& r)
+    {
+        const ll_topo& tp = ctx->topo;
+        mmat_resume_args ra{};
+        mmat_args& a = ra.m;
+        a.params = static_cast<const float*>(h.params), a.layouts = static_cast<const ll_layout<float>*>(h.layouts);
+        a.n_layouts = h.n_layouts, a.max_steps = h.max_steps, a.n_members = h.n_members;
+        a.fitness = h.fitness, a.lr = h.lr, a.steps = h.steps, a.ep_steps = h.ep_steps, a.ep_fit = h.ep_fit;
+        a.queue = h.queue + 2; // the tile kernel uses words 0 (work counter) and 1 (error flag)
+        a.p_dev = tp.p_dev;
+        for (int l = 0; l < tp.n_layers; ++l) a.w_off[l] = tp.w_off[l], a.b_off[l] = tp.b_off[l], a.out_pad[l] = tp.out_pad[l];
+        ra.r      = r;
+        auto kern = ll_episode_mmat_resume_kernel<N, WPM>;
+        int max_smem = 0;
+        LL_CUDA(ctx, cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, ctx->device));
+        constexpr int pairs = resume_pairs<N>();
+        const size_t smem   = (size_t)pairs * N::total * 4 + pairs * sizeof(pair_ctl);
+        if ((size_t)max_smem < smem) return ll_fail(ctx, LL_EINVAL, "mmat resume kernel: the member row does not fit in shared memory");
+        LL_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ll_env<float> env;
+        ll_make_env<float>(ctx->env_cfg, 1, &env);
+        LL_CUDA(ctx, cudaMemsetAsync(a.queue, 0, sizeof(unsigned int), ctx->stream));
+        const unsigned long long ctas_needed = (h.n_members + pairs - 1) / pairs;
+        const unsigned int grid = (unsigned int)std::max<unsigned long long>(1, std::min<unsigned long long>((unsigned long long)ctx->sm_count, ctas_needed));
+        kern<<<grid, 32 * WPM * pairs, smem, ctx->stream>>>(env, ra);
+        LL_CUDA(ctx, cudaGetLastError());
+        return LL_OK;
+    }
+} // namespace
+
+int ll_launch_episode_mmat_resume(ll_ctx* ctx, const ll_episode_args& a, const ll_resume_args& r)
+{
+    const ll_topo& tp = ctx->topo;
+    const bool three = t_env_int("LL_TC05_RESUME_WARPS", LL_TC05_RESUME_WARPS_DEFAULT) >= 3;
+    if (t_same_net<tnet_32_128_32>(tp)) return three ? launch_mmat_resume_t<tnet_32_128_32, 3>(ctx, a, r) : launch_mmat_resume_t<tnet_32_128_32, 2>(ctx, a, r);
+    if (t_same_net<tnet_16_64_32>(tp)) return three ? launch_mmat_resume_t<tnet_16_64_32, 3>(ctx, a, r) : launch_mmat_resume_t<tnet_16_64_32, 2>(ctx, a, r);
+    return ll_fail(ctx, LL_EINVAL, "mmat resume kernel: topology not instantiated");
+}
 
 // Same coverage as ll_mma_applicable (the sample_runs topologies with tanh).  Which of the two tensor-core kernels runs is
 // decided in ll_episode.cu (ll_launch_episode): LL_FAST_KERNEL = mmat | mma | ffma forces one.

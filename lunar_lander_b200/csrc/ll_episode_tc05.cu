@@ -36,7 +36,10 @@
 #include "ll_tc05.cuh"
 
 #ifndef LL_TC05_CUT_DEFAULT
-#define LL_TC05_CUT_DEFAULT 16
+#define LL_TC05_CUT_DEFAULT 24
+#endif
+#ifndef LL_TC05_RESUME_MMAT_DEFAULT
+#define LL_TC05_RESUME_MMAT_DEFAULT true
 #endif
 #ifndef LL_TC05_SPLIT_DEFAULT
 #define LL_TC05_SPLIT_DEFAULT 0
@@ -588,8 +591,8 @@ namespace
         }
     };
 
-    // LL_TC05_CUT: a member leaves its 64-row tile for the 16-row straggler kernel when at most this many episodes are still running
-    // (0 = never; default 16 = one mma.sync tile)
+    // LL_TC05_CUT: a member leaves its 64-row tile for the straggler pass when at most this many episodes are still running
+    // (0 = never; default 24: three 8-column tiles' worth for the two warps that share the member in ll_episode_mmat_resume_kernel)
     int env_cut()
     {
         const char* v = getenv("LL_TC05_CUT");
@@ -647,7 +650,12 @@ namespace
         LL_CUDA(ctx, cudaMemsetAsync(h.queue, 0, 2 * sizeof(unsigned int), ctx->stream));
         kern<<<grid, QUAD_THREADS * NQ, smem, ctx->stream>>>(env, a);
         LL_CUDA(ctx, cudaGetLastError());
-        if (cut > 0 && !getenv("LL_TC05_DEBUG_NORESUME")) return ll_launch_episode_mma_resume(ctx, h, a.resume); // debug switch: time the tile kernel alone (results incomplete)
+        if (cut > 0 && !getenv("LL_TC05_DEBUG_NORESUME")) // debug switch: time the tile kernel alone (results incomplete)
+        { // LL_TC05_RESUME = mma (16-row tile, slots on M) | mmat (8-column tile, slots on N)
+            const char* which = getenv("LL_TC05_RESUME");
+            const bool n_side = which && *which ? !strcmp(which, "mmat") : LL_TC05_RESUME_MMAT_DEFAULT;
+            return n_side ? ll_launch_episode_mmat_resume(ctx, h, a.resume) : ll_launch_episode_mma_resume(ctx, h, a.resume);
+        }
         return LL_OK;
     }
 

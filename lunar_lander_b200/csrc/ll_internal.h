@@ -197,7 +197,8 @@ struct ll_resume_args
     unsigned int* list;            // members with records, in arrival order
     unsigned int* n;               // number of entries of `list`
 };
-int ll_launch_episode_mma_resume(ll_ctx* ctx, const ll_episode_args& a, const ll_resume_args& r); // ll_episode_mma.cu
+int ll_launch_episode_mma_resume(ll_ctx* ctx, const ll_episode_args& a, const ll_resume_args& r); // ll_episode_mma.cu: 16-row tile
+int ll_launch_episode_mmat_resume(ll_ctx* ctx, const ll_episode_args& a, const ll_resume_args& r); // ll_episode_mmat.cu: 8-column tile
 int ll_launch_episode_tc05(ll_ctx* ctx, const ll_episode_args& a); // ll_episode_tc05.cu
 bool ll_tc05_applicable(const ll_ctx* ctx, int n_layouts);
 // default choice of the tcgen05 kernel: where it applies (17..64 layouts, the instantiated topologies) and the shard fills its 6 member

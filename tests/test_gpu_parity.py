@@ -723,15 +723,19 @@ def test_fast_tcgen05_kernel_tracks_exact_fp32(ll, po, topo, n_layouts, pop, mon
     # tc05_nocut = the tile kernel alone (LL_TC05_CUT=0)
     # tc05_s0/1/2 = LL_TC05_SPLIT variants (how a 128-wide layer's instructions are overlapped with its own epilogue): same products in
     # the same order, so bit-identical results
-    for tag, kern, cut, split in (("tc05", "tc05", "16", None), ("tc05", "tc05", "16", None), ("tc05_nocut", "tc05", "0", None), ("mma", "mma", "16", None),
-                                  ("tc05_s0", "tc05", "16", "0"), ("tc05_s1", "tc05", "16", "1"), ("tc05_s2", "tc05", "16", "2"),
-                                  ("tc05_cut40", "tc05", "40", None), ("tc05_cut5", "tc05", "5", None)):
+    # tc05_n* = the straggler pass on the N-side kernel (LL_TC05_RESUME=mmat: 8-column tile refilled from the waiting records)
+    for tag, kern, cut, split, resume in (("tc05", "tc05", "16", None, None), ("tc05", "tc05", "16", None, None), ("tc05_nocut", "tc05", "0", None, None),
+                                          ("mma", "mma", "16", None, None), ("tc05_s0", "tc05", "16", "0", None), ("tc05_s1", "tc05", "16", "1", None),
+                                          ("tc05_s2", "tc05", "16", "2", None), ("tc05_cut40", "tc05", "40", None, "mma"), ("tc05_cut5", "tc05", "5", None, "mma"),
+                                          ("tc05_n16", "tc05", "16", None, "mmat"), ("tc05_n16", "tc05", "16", None, "mmat"), ("tc05_n8", "tc05", "8", None, "mmat"),
+                                          ("tc05_n40", "tc05", "40", None, "mmat"), ("tc05_m16", "tc05", "16", None, "mma")):
         monkeypatch.setenv("LL_FAST_KERNEL", kern)
         monkeypatch.setenv("LL_TC05_CUT", cut)
-        if split is None:
-            monkeypatch.delenv("LL_TC05_SPLIT", raising=False)
-        else:
-            monkeypatch.setenv("LL_TC05_SPLIT", split)
+        for var, val in (("LL_TC05_SPLIT", split), ("LL_TC05_RESUME", resume)):
+            if val is None:
+                monkeypatch.delenv(var, raising=False)
+            else:
+                monkeypatch.setenv(var, val)
         eng, cfg = _engine(ll, sizes, pop, 32, mode=1)
         eng.set_members(0, members)
         fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
@@ -745,7 +749,7 @@ def test_fast_tcgen05_kernel_tracks_exact_fp32(ll, po, topo, n_layouts, pop, mon
             assert np.array_equal(got[tag][2], fit) and np.array_equal(got[tag][0], ep_steps)  # deterministic
         got[tag] = (ep_steps, flags, fit, lr)
         eng.close()
-    for v in ("tc05", "tc05_cut40", "tc05_cut5"):  # hand-over thresholds above 16 refill the straggler kernel's 16 rows
+    for v in ("tc05", "tc05_cut40", "tc05_cut5", "tc05_n16", "tc05_n8", "tc05_n40", "tc05_m16"):  # thresholds above the tile size refill the straggler tile
         assert np.mean(got[v][0] == got["tc05_nocut"][0]) >= 0.98, v
     for v in ("tc05_s0", "tc05_s1", "tc05_s2"):
         assert np.array_equal(got[v][0], got["tc05"][0]) and np.array_equal(got[v][2], got["tc05"][2]), v
