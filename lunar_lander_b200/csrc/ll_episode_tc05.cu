@@ -136,11 +136,30 @@ namespace
     // byte offset of element (n, k) of a K-major no-swizzle operand with `rows` rows: 8 x 16-byte core matrices, 8-row groups contiguous
     __device__ __forceinline__ int op_off(int n, int k, int rows) { return (n >> 3) * 128 + (k >> 3) * (rows * 16) + (n & 7) * 16 + (k & 7) * 2; }
 
+    // packed fp32 pairs (FADD2: one issue slot for two IEEE round-to-nearest adds — same results as two FADDs)
+#ifndef LL_TC05_PACKED
+#define LL_TC05_PACKED 1
+#endif
+    __device__ __forceinline__ void add2(float& a0, float& a1, float b0, float b1, bool negate_b = false)
+    {
+#if LL_TC05_PACKED
+        unsigned long long a, b, c;
+        asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(a0), "f"(a1));
+        asm("mov.b64 %0, {%1, %2};" : "=l"(b) : "f"(b0), "f"(b1));
+        if (negate_b) asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(c) : "l"(a), "l"(b));
+        else asm("add.rn.f32x2 %0, %1, %2;" : "=l"(c) : "l"(a), "l"(b));
+        asm("mov.b64 {%0, %1}, %2;" : "=f"(a0), "=f"(a1) : "l"(c));
+#else
+        a0 = negate_b ? a0 - b0 : a0 + b0, a1 = negate_b ? a1 - b1 : a1 + b1;
+#endif
+    }
+
     __device__ __forceinline__ void split_pair(float x0, float x1, uint32_t& hi, uint32_t& lo)
     { // hi = leading 11 significant bits (exact in f16), lo = x - hi (exact in fp32, |lo| < 2^-11 |x|): see ll_episode_mma.cu
         const float h0 = __uint_as_float(__float_as_uint(x0) & 0xffffe000u), h1 = __uint_as_float(__float_as_uint(x1) & 0xffffe000u);
         const __half2 ph = __floats2half2_rn(h0, h1);
-        const __half2 pl = __floats2half2_rn(x0 - h0, x1 - h1);
+        add2(x0, x1, h0, h1, true);
+        const __half2 pl = __floats2half2_rn(x0, x1);
         hi = *reinterpret_cast<const uint32_t*>(&ph);
         lo = *reinterpret_cast<const uint32_t*>(&pl);
     }
@@ -269,7 +288,8 @@ namespace
                 if constexpr (L > 0)
                 { // (layer 0's bias rides in its K block)
                     const float4 b = sb[(c * CH) / 4 + j];
-                    z0 += b.x, z1 += b.y, z2 += b.z, z3 += b.w;
+                    add2(z0, z1, b.x, b.y);
+                    add2(z2, z3, b.z, b.w);
                 }
                 const float x0 = ll_tanh_approx(z0), x1 = ll_tanh_approx(z1), x2 = ll_tanh_approx(z2), x3 = ll_tanh_approx(z3);
                 split_pair(x0, x1, hi[2 * j], lo[2 * j]);
