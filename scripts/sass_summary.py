@@ -9,10 +9,11 @@ import subprocess
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "lunar_lander_b200", "libll_gpu.so")
-WANT = [("tc05_32_128_32", r"ll_episode_tc05_kernel.*Li5ELi32ELi128ELi32ELi4E"), ("mma_resume_32_128_32", r"ll_episode_mma_resume_kernel.*Li5ELi32ELi128ELi32ELi4E"),
+WANT = [("tc05_32_128_32", r"ll_episode_tc05_kernel.*Li5ELi32ELi128ELi32ELi4EEEELi0E"), ("mma_resume_32_128_32", r"ll_episode_mma_resume_kernel.*Li5ELi32ELi128ELi32ELi4E"),
+        ("mmat_resume_32_128_32", r"ll_episode_mmat_resume_kernel.*Li5ELi32ELi128ELi32ELi4EEEELi2E"), ("exactw_f64_16_16", r"ll_episode_exactw_kernelId.*Li5ELi16ELi16ELi4E"),
         ("mma_32_128_32", r"ll_episode_mma_kernel.*Li5ELi32ELi128ELi32ELi4E.*Li0E"), ("mmat_16_64_32", r"ll_episode_mmat_kernel.*Li5ELi16ELi64ELi32ELi4E.*Li1E"),
         ("warp_8_16_8", r"ll_episode_warp_kernel.*Li5ELi8ELi16ELi8ELi4E"), ("exact_f64", r"ll_episode_kernel.*IdLi0E"),
-        ("create_population_f32", r"ll_create_population_f32_kernel")]
+        ("create_population_f32_fast", r"ll_create_population_f32_kernelILb1E"), ("create_population_f32_exact", r"ll_create_population_f32_kernelILb0E")]
 KEY = ["UTCHMMA", "UTCBAR", "LDTM", "STTM", "UBLKCP", "UTMALDG", "HMMA", "MOVM", "MUFU.TANH", "MUFU", "SYNCS", "BAR.SYNC", "FFMA", "DFMA", "DMUL", "DADD", "SHFL", "LDS", "STS"]
 
 sass = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True).stdout
