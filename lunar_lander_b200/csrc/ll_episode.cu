@@ -670,7 +670,7 @@ const char* ll_episode_kernel_name(const ll_ctx* ctx, int n_layouts)
     }
     if (ctx->precision == 64) return "ll_episode_kernel<double,exact>";
     if (ctx->mode == LL_MODE_FAST && ll_use_warp(ctx, n_layouts)) return "ll_episode_warp_kernel (warp per member, FFMA + shuffles)";
-    if (ctx->mode == LL_MODE_FAST && ll_use_tc05(ctx, n_layouts)) return "ll_episode_tc05_kernel (tcgen05 + TMEM; straggler pass mma.sync)";
+    if (ctx->mode == LL_MODE_FAST && ll_use_tc05(ctx, n_layouts)) return "ll_episode_tc05_kernel (tcgen05 + TMEM; stragglers: mma.sync)";
     if (ctx->mode == LL_MODE_FAST && ll_use_mmat(ctx, n_layouts)) return "ll_episode_mmat_kernel (3 x f16-split mma.sync, slots on N)";
     if (ctx->mode == LL_MODE_FAST && ll_mma_applicable(ctx, n_layouts)) return "ll_episode_mma_kernel (3 x f16-split mma.sync)";
     if (ctx->mode == LL_MODE_FAST) return ll_fast_applicable(ctx, n_layouts) ? "ll_episode_fast_kernel (slot-pool GEMM)" : "ll_episode_kernel<float,fast>";
