@@ -257,6 +257,25 @@ def hmma_flop_per_step(sizes, transposed=False):
     return tiles * 3 * 2 * 16 * 8 * 16 / 16.0
 
 
+def tc05_flop_per_step(sizes):
+    """tcgen05.mma flop per live row (= lander step) of ll_episode_tc05_kernel: per layer (K blocks of 16) x 3 split products (the first
+    layer packs its three products into 2 instructions) x N padded (hidden layers to 16, the output layer to 8) x K = 16 x 2."""
+    n_layers, flop = len(sizes) - 1, 0
+    for l in range(n_layers):
+        npad = 8 if l == n_layers - 1 else (sizes[l + 1] + 15) // 16 * 16
+        instr = 2 if l == 0 else 3 * ((sizes[l] + 15) // 16)
+        flop += instr * npad * 16 * 2
+    return flop
+
+
+def measured_bf16_peak(key="bf16_tflops"):
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        return float(json.load(open(p))[key])
+    except Exception:
+        return None
+
+
 class Peaks:
     """Roofline denominators measured on THIS device (rank-local), each once per run: FMA chains (ll_microbench_fma), mean over a
     0.25 s burst and over a 3 s loop, with the SM clock the same thread saw (cycles / %globaltimer ns)."""
@@ -473,7 +492,15 @@ def measure(ctx, workload, steps, warmup, min_timed_s=1.5, e2e_steps=None, cpu_s
                                      "mma.sync.m16n8k16.f16 rate",
                              "hmma_flop_per_lander_step": hmma_flop_per_step(sizes, "mmat" in kernel),
                              "achieved_live_rows": steps_local * hmma_flop_per_step(sizes, "mmat" in kernel) / (episode_ms_max * 1e-3) / 1e12 if episode_ms_max > 0 else None,
-                             "peak": hmma_peak, "unit": "TFLOP/s"} if "_mma" in kernel else None),
+                             "peak": hmma_peak, "unit": "TFLOP/s"} if "_mma" in kernel else
+                            {"note": "explains the FMA-roofline fraction: flop the tcgen05 tile kernel issues per LIVE lander step (3 f16-split products "
+                                     "on K = 16 blocks, N padded to 8 / 16; M = 64 tiles whose dead rows are not counted; the straggler pass's steps "
+                                     "are counted at the same rate although they run on mma.sync) against the measured dense bf16 rate of "
+                                     "MEASURED_PEAKS.json - an M = 64 tile can use at most half of that",
+                             "mma_flop_per_lander_step": tc05_flop_per_step(sizes),
+                             "achieved_live_rows": steps_local * tc05_flop_per_step(sizes) / (episode_ms_max * 1e-3) / 1e12 if episode_ms_max > 0 else None,
+                             "peak": measured_bf16_peak(), "peak_sustained": measured_bf16_peak("bf16_tflops_sustained"), "unit": "TFLOP/s"}
+                            if "_tc05_" in kernel else None),
             "roofline_ga": {"bound": "hbm", "achieved": ga_gbs, "peak": hbm_peak, "unit": "GB/s",
                             "frac": ga_gbs / hbm_peak if hbm_peak else None, "traffic": ncu_traffic("k4_" + topo, eng.pop_local - top),
                             "kernel": ("ll_create_population_f32_kernel<fast: Philox4x32-7 + SFU Box-Muller>" if mode == 1 and precision == 32 else
