@@ -1,12 +1,13 @@
 #!/bin/bash
-# A/B of environment switches on configs[0] (16_16, 100 x 50, fp64 exact): scripts/ab_c1.sh "LL_EXACT_Q=4" "LL_EXACT_Q=32" ...
+# A/B of environment switches on one of the small workloads: scripts/ab_wl.sh c2 "LL_WARP_HALF=0" "LL_WARP_HALF=1" ...
+WL=$1; shift
 mkdir -p gpurun_out
 n=0
 for setting in "$@"; do
   n=$((n + 1))
-  env $setting timeout 300 python bench.py --workload c1 --steps 20 --warmup 3 --no-cpu-baseline --no-extras --no-invariance --e2e-steps 3 \
-      > gpurun_out/abc1_$n.json 2> gpurun_out/abc1_$n.err || { echo "[$setting] failed"; tail -5 gpurun_out/abc1_$n.err; }
-  python - "$setting" gpurun_out/abc1_$n.json <<'PY'
+  env $setting timeout 300 python bench.py --workload $WL --steps 20 --warmup 3 --auto-steps --no-cpu-baseline --no-extras --no-invariance --e2e-steps 3 \
+      > gpurun_out/abwl_$n.json 2> gpurun_out/abwl_$n.err || { echo "[$setting] failed"; tail -5 gpurun_out/abwl_$n.err; }
+  python - "$setting" gpurun_out/abwl_$n.json <<'PY'
 import json, sys
 try:
     d = json.loads(open(sys.argv[2]).read().strip().splitlines()[-1])

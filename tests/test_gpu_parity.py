@@ -719,8 +719,8 @@ def test_fast_tcgen05_kernel_tracks_exact_fp32(ll, po, topo, n_layouts, pop, mon
         spad, lpad, d = np.tile(spad, 2), np.tile(lpad, 2), np.tile(d, 2)
     spad, lpad, d = spad[:n_layouts], lpad[:n_layouts], d[:n_layouts]
     got = {}
-    # tc05 = tile kernel + hand-over of a member's last <= 16 running episodes to the 16-row mma.sync kernel (the default);
-    # tc05_nocut = the tile kernel alone (LL_TC05_CUT=0)
+    # tc05 = tile kernel + hand-over of a member's last <= 16 running episodes to the straggler pass (the default pass; the default
+    # threshold is 24: tc05_n24); tc05_nocut = the tile kernel alone (LL_TC05_CUT=0)
     # tc05_s0/1/2 = LL_TC05_SPLIT variants (how a 128-wide layer's instructions are overlapped with its own epilogue): same products in
     # the same order, so bit-identical results
     # tc05_n* = the straggler pass on the N-side kernel (LL_TC05_RESUME=mmat: 8-column tile refilled from the waiting records)
@@ -728,7 +728,7 @@ def test_fast_tcgen05_kernel_tracks_exact_fp32(ll, po, topo, n_layouts, pop, mon
                                           ("mma", "mma", "16", None, None), ("tc05_s0", "tc05", "16", "0", None), ("tc05_s1", "tc05", "16", "1", None),
                                           ("tc05_s2", "tc05", "16", "2", None), ("tc05_cut40", "tc05", "40", None, "mma"), ("tc05_cut5", "tc05", "5", None, "mma"),
                                           ("tc05_n16", "tc05", "16", None, "mmat"), ("tc05_n16", "tc05", "16", None, "mmat"), ("tc05_n8", "tc05", "8", None, "mmat"),
-                                          ("tc05_n40", "tc05", "40", None, "mmat"), ("tc05_m16", "tc05", "16", None, "mma")):
+                                          ("tc05_n40", "tc05", "40", None, "mmat"), ("tc05_m16", "tc05", "16", None, "mma"), ("tc05_n24", "tc05", "24", None, None)):
         monkeypatch.setenv("LL_FAST_KERNEL", kern)
         monkeypatch.setenv("LL_TC05_CUT", cut)
         for var, val in (("LL_TC05_SPLIT", split), ("LL_TC05_RESUME", resume)):
@@ -749,7 +749,7 @@ def test_fast_tcgen05_kernel_tracks_exact_fp32(ll, po, topo, n_layouts, pop, mon
             assert np.array_equal(got[tag][2], fit) and np.array_equal(got[tag][0], ep_steps)  # deterministic
         got[tag] = (ep_steps, flags, fit, lr)
         eng.close()
-    for v in ("tc05", "tc05_cut40", "tc05_cut5", "tc05_n16", "tc05_n8", "tc05_n40", "tc05_m16"):  # thresholds above the tile size refill the straggler tile
+    for v in ("tc05", "tc05_cut40", "tc05_cut5", "tc05_n16", "tc05_n8", "tc05_n40", "tc05_m16", "tc05_n24"):  # thresholds above the tile size refill the straggler tile
         assert np.mean(got[v][0] == got["tc05_nocut"][0]) >= 0.98, v
     for v in ("tc05_s0", "tc05_s1", "tc05_s2"):
         assert np.array_equal(got[v][0], got["tc05"][0]) and np.array_equal(got[v][2], got["tc05"][2]), v
