@@ -148,6 +148,9 @@ extern "C" const char* ll_last_error(const ll_ctx* ctx) { return ctx && !ctx->er
         if (!(ctx)) return ll_fail(nullptr, LL_EINVAL, "null context");                                              \
         cudaSetDevice((ctx)->device);                                                                                \
     } while (0)
+// kernels of ll_launch_topk: keys + 12 radix passes + collect + sort, or candidates + sort for populations of at most LL_MAX_TOP members
+static int topk_launches(const ll_ctx* ctx) { return ctx->pop_local <= LL_MAX_TOP ? 2 : 15; }
+
 #define LL_TRY(call)                                                                                                 \
     do {                                                                                                             \
         int rc__ = (call);                                                                                           \
@@ -361,7 +364,7 @@ static int install_elites_from_idx(ll_ctx* ctx, unsigned int n)
 static int device_topk(ll_ctx* ctx, unsigned int k)
 {
     if (!ctx->have_results) return ll_fail(ctx, LL_EINVAL, "selection needs the results of ll_evaluate");
-    scope s(ctx, CLS_SELECT, 1 + 12 + 1 + 1 + 1);
+    scope s(ctx, CLS_SELECT, topk_launches(ctx) + 1);
     LL_TRY(ll_launch_topk(ctx, k));
     ll_cand_to_idx_kernel<<<(k + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_cand, k, ctx->d_elite_idx);
     LL_CUDA(ctx, cudaGetLastError());
@@ -389,7 +392,7 @@ extern "C" int ll_select(ll_ctx* ctx, const uint64_t* sorted_idx, uint64_t n_sor
     else
     { // every rank makes the same call: all-gather of the local top-k + merge (no indices given), row gather + all-reduce
         if (!sorted_idx && !ctx->have_results) return ll_fail(ctx, LL_EINVAL, "selection needs the results of ll_evaluate");
-        scope s(ctx, CLS_SELECT, sorted_idx ? 1 : 1 + 12 + 1 + 1 + 4);
+        scope s(ctx, CLS_SELECT, sorted_idx ? 1 : topk_launches(ctx) + 4);
         LL_TRY(ll_comm_select(ctx, sorted_idx != nullptr));
     }
     if (elite_idx_out)
@@ -588,7 +591,7 @@ extern "C" int ll_step_generation(ll_ctx* ctx, int32_t max_steps, int elitism, l
     }
     else
     { // K2 -> NCCL all-gather -> merge -> K3 -> NCCL all-reduce, all on the context's stream: no host round trip
-        scope s(ctx, CLS_SELECT, 1 + 12 + 1 + 1 + 4);
+        scope s(ctx, CLS_SELECT, topk_launches(ctx) + 4);
         LL_TRY(ll_comm_select(ctx, false));
     }
     {

@@ -299,6 +299,16 @@ namespace
         st->hist[threadIdx.x] = 0u;
     }
 
+    // small populations (n <= LL_MAX_TOP): every member is a candidate, the single-block sort below does the whole selection
+    // (2 launches instead of 15: the reference's own population sizes are launch-latency territory)
+    __global__ void ll_all_candidates_kernel(const double* __restrict__ fit, unsigned int n, unsigned long long first_global, ll_cand* __restrict__ cand)
+    {
+        const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+        if (i >= n) return;
+        cand[i].fitness = __longlong_as_double((long long)ll_orderable(fit[i])); // orderable bits, decoded by the sort kernel
+        cand[i].index   = first_global + i;
+    }
+
     // after 12 passes (prefix_hi, prefix_lo) IS the k-th smallest composite key: collect everything <= it
     __global__ void ll_select_collect_kernel(const unsigned long long* __restrict__ keys, unsigned long long n, unsigned long long first_global,
                                              ll_select_state* st, ll_cand* cand, unsigned int cap)
@@ -435,15 +445,24 @@ int ll_launch_topk(ll_ctx* ctx, unsigned int k)
     const unsigned long long n = ctx->pop_local;
     if (k == 0 || k > n || k > LL_MAX_TOP) return ll_fail(ctx, LL_EINVAL, "top-k: k out of range");
     const unsigned int blocks = (unsigned int)((n + 255) / 256);
-    ll_keys_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->d_fitness, n, ctx->d_keys, ctx->d_sel, k);
-    unsigned int hb = blocks < (unsigned int)(ctx->sm_count * 8) ? blocks : (unsigned int)(ctx->sm_count * 8);
-    for (int pass = 0; pass < 12; ++pass) ll_select_hist_kernel<<<hb, 256, 0, ctx->stream>>>(ctx->d_keys, n, pass, ctx->d_sel);
-    ll_select_collect_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->d_keys, n, ctx->first_global, ctx->d_sel, ctx->d_cand, LL_MAX_TOP);
+    unsigned int n_sort       = k; // entries the sort kernel orders
+    if (n <= LL_MAX_TOP)
+    {
+        ll_all_candidates_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->d_fitness, (unsigned int)n, ctx->first_global, ctx->d_cand);
+        n_sort = (unsigned int)n;
+    }
+    else
+    {
+        ll_keys_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->d_fitness, n, ctx->d_keys, ctx->d_sel, k);
+        unsigned int hb = blocks < (unsigned int)(ctx->sm_count * 8) ? blocks : (unsigned int)(ctx->sm_count * 8);
+        for (int pass = 0; pass < 12; ++pass) ll_select_hist_kernel<<<hb, 256, 0, ctx->stream>>>(ctx->d_keys, n, pass, ctx->d_sel);
+        ll_select_collect_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->d_keys, n, ctx->first_global, ctx->d_sel, ctx->d_cand, LL_MAX_TOP);
+    }
     unsigned int np2 = 2;
-    while (np2 < k) np2 <<= 1;
+    while (np2 < n_sort) np2 <<= 1;
     const size_t smem = (size_t)np2 * 16;
     LL_CUDA(ctx, cudaFuncSetAttribute(ll_select_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    ll_select_sort_kernel<<<1, np2 / 2 < 1024 ? (np2 / 2 < 32 ? 32 : np2 / 2) : 1024, smem, ctx->stream>>>(ctx->d_cand, k, np2);
+    ll_select_sort_kernel<<<1, np2 / 2 < 1024 ? (np2 / 2 < 32 ? 32 : np2 / 2) : 1024, smem, ctx->stream>>>(ctx->d_cand, n_sort, np2);
     LL_CUDA(ctx, cudaGetLastError());
     return LL_OK;
 }
