@@ -213,3 +213,30 @@ def test_cpp_trainer_on_two_gpus_prints_the_one_gpu_log(tmp_path, suffix, mode, 
     assert files == sorted(os.listdir(os.path.join(two, "data"))) and files
     for name in files:
         assert weight_file_body(os.path.join(one, "data", name)) == weight_file_body(os.path.join(two, "data", name)), name
+
+
+def test_python_trainer_on_two_ranks_prints_the_one_rank_log(tmp_path, built):
+    """torchrun --nproc-per-node 2 -m lunar_lander_b200.trainer (one process per GPU, the communicator behind the ABI: sharded.py
+    broadcasts the NCCL id, ll_comm_init, ll_step_generation on shards) against the same trainer on one rank: same log, same
+    checkpoint files, bit for bit (exact mode).  Runs only where two GPUs are visible."""
+    import sys
+    if _gpu_count() < 2:
+        pytest.skip("needs two GPUs")
+    ov = dict(SMALL)
+    ov.update({"NNConfig.hlayers": "16,64,32", "NNConfig.epochs": 5, "NNConfig.population_size": 999, "NNTrainingCfg.layout_nb": 8,
+               "NNConfig.save_interval": 2, "GpuCfg.mode": "exact"})
+    one, two = str(tmp_path / "one"), str(tmp_path / "two")
+    write_config(one, **ov)
+    write_config(two, **ov)
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    p1 = subprocess.run([sys.executable, "-m", "lunar_lander_b200.trainer", "--float"], cwd=one, capture_output=True, text=True, timeout=600, env=env)
+    p2 = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                         "--master-port", "29533", "-m", "lunar_lander_b200.trainer", "--float"], cwd=two, capture_output=True, text=True, timeout=900, env=env)
+    assert p1.returncode == 0, p1.stderr[-2000:]
+    assert p2.returncode == 0, p2.stderr[-2000:]
+    banner = re.compile(r"^NCCL version .*\n", re.M)
+    assert normalise(p1.stdout) == banner.sub("", normalise(p2.stdout))
+    files = sorted(os.listdir(os.path.join(one, "data")))
+    assert files == sorted(os.listdir(os.path.join(two, "data"))) and files
+    for name in files:
+        assert weight_file_body(os.path.join(one, "data", name)) == weight_file_body(os.path.join(two, "data", name)), name
