@@ -482,7 +482,7 @@ namespace
         const int by_smem = (227 * 1024 - 256) / (N::total * 4);
         return by_smem >= 6 ? 6 : (by_smem < 1 ? 1 : by_smem);
     }
-    // WPM warps share one member (LL_TC05_RESUME_WARPS: 2 or 3)
+    // WPM warps share one member
     template <int WPM> __device__ __forceinline__ void pair_sync(int pair) { asm volatile("bar.sync %0, %1;" : : "r"(1 + pair), "n"(32 * WPM) : "memory"); }
 
     template <class N, int WPM>
@@ -661,9 +661,6 @@ namespace
     }
 } // namespace
 
-#ifndef LL_TC05_RESUME_WARPS_DEFAULT
-#define LL_TC05_RESUME_WARPS_DEFAULT 2
-#endif
 namespace
 {
     template <class N, int WPM> int launch_mmat_resume_t(ll_ctx* ctx, const ll_episode_args& h, const ll_resume_args& r)
@@ -699,9 +696,9 @@ namespace
 int ll_launch_episode_mmat_resume(ll_ctx* ctx, const ll_episode_args& a, const ll_resume_args& r)
 {
     const ll_topo& tp = ctx->topo;
-    const bool three = t_env_int("LL_TC05_RESUME_WARPS", LL_TC05_RESUME_WARPS_DEFAULT) >= 3;
-    if (t_same_net<tnet_32_128_32>(tp)) return three ? launch_mmat_resume_t<tnet_32_128_32, 3>(ctx, a, r) : launch_mmat_resume_t<tnet_32_128_32, 2>(ctx, a, r);
-    if (t_same_net<tnet_16_64_32>(tp)) return three ? launch_mmat_resume_t<tnet_16_64_32, 3>(ctx, a, r) : launch_mmat_resume_t<tnet_16_64_32, 2>(ctx, a, r);
+    // two warps per staged member (one: 204.0 ms on the 32 768-member sample, two: 201.4, three: 202.4 at 92 registers)
+    if (t_same_net<tnet_32_128_32>(tp)) return launch_mmat_resume_t<tnet_32_128_32, 2>(ctx, a, r);
+    if (t_same_net<tnet_16_64_32>(tp)) return launch_mmat_resume_t<tnet_16_64_32, 2>(ctx, a, r);
     return ll_fail(ctx, LL_EINVAL, "mmat resume kernel: topology not instantiated");
 }
 

@@ -41,9 +41,6 @@
 #ifndef LL_TC05_RESUME_MMAT_DEFAULT
 #define LL_TC05_RESUME_MMAT_DEFAULT true
 #endif
-#ifndef LL_TC05_SPLIT_DEFAULT
-#define LL_TC05_SPLIT_DEFAULT 0
-#endif
 
 namespace
 {
@@ -128,7 +125,7 @@ namespace
         unsigned long long member[2];     // member flown by half 0 / 1 (~0ull: none)
         unsigned int live[4];             // per warp: ballot of slots whose episode is running (low 16 bits half 0, high 16 half 1)
         int exhausted[2];                 // the queue is empty for this half
-        unsigned long long mbar2;         // second commit target: the upper N half of a wide layer (step_loop, SPLIT >= 1)
+        int pad_[2];
         double ep_fit[2][SLOTS];          // per-slot episode results of the member in flight
         int ep_meta[2][SLOTS];            // steps | flags << 28
     };
@@ -204,17 +201,13 @@ namespace
 
     // tcgen05.mma chain of layer L for one half: D[64 x npad] (+)= X[64 x kpad] * W^T, three split products per K = 16 block.
     // tq = TMEM address of the quad's column 0 at the half's lane offset (0 or 16); sm = shared address of the member's region.
-    // NH / NI: the layer's output neurons go in NH equal parts (separate instructions on separate D columns, same staged operand: part NI
-    // starts NI * NP / NH rows into W, i.e. (rows / 8) * 128 bytes in the core-matrix layout; the K stride LBO is that of the whole operand)
-    template <class N, int L, int NH = 1, int NI = 0>
-    __device__ __forceinline__ void issue_layer(uint32_t tq, uint32_t sm, int kc_begin = 0, int kc_end = N::kpad(L) / 16)
+    template <class N, int L> __device__ __forceinline__ void issue_layer(uint32_t tq, uint32_t sm)
     {
-        constexpr int KP = N::kpad(L), NP = N::npad(L), NPART = NP / NH;
-        static_assert(NP % NH == 0 && NPART % 8 == 0, "output split");
-        constexpr uint32_t idesc = tc05::idesc_f16(64, NPART, 0, 0);
+        constexpr int KP = N::kpad(L), NP = N::npad(L);
+        constexpr uint32_t idesc = tc05::idesc_f16(64, NP, 0, 0);
         constexpr uint32_t LBO = NP * 16, SBO = 128;
-        const uint32_t d   = tq + N::dcol(L) + NI * NPART;
-        const uint32_t whi = sm + N::w_off(L) + NI * (NPART / 8) * 128, wlo = whi + N::w_bytes(L);
+        const uint32_t d   = tq + N::dcol(L);
+        const uint32_t whi = sm + N::w_off(L), wlo = whi + N::w_bytes(L);
         if constexpr (L == 0)
         { // one K block holds hi(state), 1, lo(state): W_hi covers X_hi*W_hi + bias_hi + X_lo*W_hi, W_lo adds X_hi*W_lo + bias_lo
             const uint32_t x0 = tq + N::x0col;
@@ -228,7 +221,6 @@ namespace
 #pragma unroll
             for (int kc = 0; kc < KP / 16; ++kc)
             {
-                if (kc < kc_begin || kc >= kc_end) continue;
                 const int k0 = 16 * kc;
                 const uint32_t a_hi = xin + (k0 / CH) * CH + (k0 % CH) / 2, a_lo = a_hi + CH / 2;
                 const uint64_t bhi = tc05::smem_desc(whi + 2 * kc * LBO, LBO, SBO), blo = tc05::smem_desc(wlo + 2 * kc * LBO, LBO, SBO);
@@ -240,13 +232,11 @@ namespace
     }
 
     // issue layers L.. of both running halves, then commit; called by ONE elected lane of the quad's first warp
-    template <class N, int L, int NH = 1, int NI = 0>
-    __device__ __forceinline__ void issue_both(uint32_t tq, uint32_t sm0, bool run0, bool run1, uint32_t mbar, int kc_begin = 0, int kc_end = N::kpad(L) / 16,
-                                               bool last = true)
+    template <class N, int L> __device__ __forceinline__ void issue_both(uint32_t tq, uint32_t sm0, bool run0, bool run1, uint32_t mbar)
     { // one half after the other (alternating the halves K block by K block measured 3 % slower: 169 vs 163 ms)
-        if (run0) issue_layer<N, L, NH, NI>(tq, sm0, kc_begin, kc_end);
-        if (run1) issue_layer<N, L, NH, NI>(tq + (16u << 16), sm0 + N::member_bytes, kc_begin, kc_end);
-        if (last) tc05::commit(mbar);
+        if (run0) issue_layer<N, L>(tq, sm0);
+        if (run1) issue_layer<N, L>(tq + (16u << 16), sm0 + N::member_bytes);
+        tc05::commit(mbar);
     }
 
     template <int CH> __device__ __forceinline__ void ld_chunk(uint32_t taddr, uint32_t (&v)[CH])
@@ -264,18 +254,12 @@ namespace
 
     // Hidden layer L, one thread = one slot: D row -> + bias -> tanh.approx -> f16 hi / lo -> back into the same TMEM columns as the
     // next layer's A operand (chunk c: hi words at column c*CH, lo words at c*CH + CH/2).
-    // PIPE: after every chunk the quad synchronises and one lane issues the next layer's K blocks that read this chunk, so that the
-    // tensor pipe works through layer L + 1 while the threads are still busy with the rest of layer L's activations.
-    // C0 / C1: the chunks [C0, C1) of the layer (C1 < 0: all of them)
-    template <class N, int L, bool PIPE, int C0 = 0, int C1 = -1>
-    __device__ __forceinline__ void epilogue_hidden(uint32_t tt, const unsigned char* __restrict__ sm, uint32_t tq = 0, uint32_t smq_a = 0, bool run0 = false,
-                                                    bool run1 = false, uint32_t mbar = 0, int q = 0, int wq = 0)
+    template <class N, int L> __device__ __forceinline__ void epilogue_hidden(uint32_t tt, const unsigned char* __restrict__ sm)
     {
         constexpr int NP = N::npad(L), CH = chunk_of<N>(L);
-        constexpr int CE = C1 < 0 ? NP / CH : C1;
         const float4* sb = reinterpret_cast<const float4*>(sm + N::b_off(L));
 #pragma unroll
-        for (int c = C0; c < CE; ++c)
+        for (int c = 0; c < NP / CH; ++c)
         {
             uint32_t v[CH];
             ld_chunk<CH>(tt + N::dcol(L) + c * CH, v);
@@ -297,18 +281,6 @@ namespace
             }
             st_words<CH / 2>(tt + N::dcol(L) + c * CH, hi);
             st_words<CH / 2>(tt + N::dcol(L) + c * CH + CH / 2, lo);
-            if constexpr (PIPE)
-            {
-                tc05::wait_st();
-                tc05::fence_before_sync();
-                tc05::named_bar_sync(1 + q, QUAD_THREADS);
-                tc05::fence_after_sync();
-                if (wq == 0)
-                {
-                    if (tc05::elect_one()) issue_both<N, L + 1>(tq, smq_a, run0, run1, mbar, c * (CH / 16), (c + 1) * (CH / 16), c + 1 == NP / CH);
-                    __syncwarp();
-                }
-            }
         }
     }
 
@@ -333,10 +305,9 @@ namespace
         return q > 3 ? 3 : (q < 1 ? 1 : q);
     }
 
-    template <class N, int V> struct step_loop;
+    template <class N> struct step_loop;
 
-    // V (LL_TC05_SPLIT): how a 128-wide layer is overlapped with its own epilogue, see step_loop
-    template <class N, int V>
+    template <class N>
     __global__ void __launch_bounds__(QUAD_THREADS* quads_per_cta<N>(), 1) ll_episode_tc05_kernel(const __grid_constant__ ll_env<float> env, const __grid_constant__ tc_args a)
     {
         static_assert(N::ok(), "topology not supported by the tcgen05 episode kernel");
@@ -349,13 +320,12 @@ namespace
         quad_ctl& ctl      = ctls[q];
         unsigned char* smq = smem + (size_t)(2 * q) * N::member_bytes; // the quad's two member regions
         unsigned char* smh = smq + h * N::member_bytes;                // this thread's half
-        const uint32_t mbar = tc05::smem_u32(&ctl.mbar), mbar2 = tc05::smem_u32(&ctl.mbar2);
+        const uint32_t mbar = tc05::smem_u32(&ctl.mbar);
 
         for (int i = tid; i < 2 * NQ * N::member_bytes / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0u; // K / N padding stays zero
         if ((tid & (QUAD_THREADS - 1)) == 0)
         {
             tc05::mbar_init(mbar, 1);
-            tc05::mbar_init(mbar2, 1);
             ctl.member[0] = ctl.member[1] = ~0ull;
             ctl.live[0] = ctl.live[1] = ctl.live[2] = ctl.live[3] = 0u;
             ctl.exhausted[0] = ctl.exhausted[1] = 0;
@@ -377,7 +347,7 @@ namespace
         double acc = 0.0;
         bool active = false, failed = false;
         unsigned long long cur_member = ~0ull; // the member this thread's half is flying (kept in a register: the leader replaces ctl.member)
-        uint32_t phase = 0, phase2 = 0;
+        uint32_t phase = 0;
         const int L    = a.n_layouts; // <= SLOTS: slot s flies layout s
 
         for (;;)
@@ -462,8 +432,7 @@ namespace
             }
             const bool run0 = ctl.member[0] != ~0ull, run1 = ctl.member[1] != ~0ull;
             if (!run0 && !run1) break; // both halves drained
-            if (step_loop<N, V>::run(env, a, ctl, tq, tt, smq_a, smh, mbar, mbar2, q, wq, h, slot, run0, run1, phase, phase2, p, cx, lpad, lpad_r, steps, acc, active,
-                                     cur_member))
+            if (step_loop<N>::run(env, a, ctl, tq, tt, smq_a, smh, mbar, q, wq, h, slot, run0, run1, phase, p, cx, lpad, lpad_r, steps, acc, active, cur_member))
             {
                 failed = true;
                 break;
@@ -477,87 +446,38 @@ namespace
 
     // One lander step of the quad: the layers in order, each = barrier -> tcgen05.mma chain (one elected lane) -> commit -> wait -> epilogue.
     // Returns true when a bounded wait timed out.
-    template <class N, int V> struct step_loop
+    // What was tried to overlap a quad's instructions with its own epilogue, measured on B200 and removed (all bit-identical to this
+    // loop): issuing a 128-wide layer as two N halves with separate commits (-0.7 %: 2 x N = 64 costs 84 pipe cycles against 74);
+    // additionally issuing the next layer's first K half between the two epilogue halves behind one more quad barrier (-3.3 %);
+    // issuing the next layer chunk by chunk from the epilogue (-7 %: a quad-wide bar.sync waits for the slowest of four warps that
+    // share their MUFU pipes with two other quads); alternating the two members K block by K block (-3 %).
+    template <class N> struct step_loop
     {
-        // does layer L's epilogue issue layer L + 1 chunk by chunk?  (only worth a barrier per chunk where there are several chunks)
-        // Measured on B200 (32_128_32, 16 384 x 50): 175 ms with the per-chunk barriers against 163 ms without — a quad-wide bar.sync
-        // waits for the slowest of four warps that share their MUFU pipes with two other quads, which costs more than the overlap
-        // returns.  Off; kept because a dedicated issuer warp fed by mbarrier arrivals would make the same overlap free.
-        static constexpr bool PIPELINE = false;
-        template <int L> static __host__ __device__ constexpr bool pipelined() { return PIPELINE && L + 1 < N::NL && N::npad(L) / chunk_of<N>(L) > 1; }
-        // V >= 1: a hidden layer of >= 128 outputs is issued as two N halves with their own commits (mbar, mbar2): the threads run the
-        //         epilogue of the lower half while the tensor pipe is still busy with the upper half (no extra barrier, 2 x N/2
-        //         instructions cost ~14 % more pipe time than one of N: 42 + 42 against 74 cycles at N = 128).
-        // V == 2: in addition the next layer's first K half (which reads only the lower half's activations) is issued between the two
-        //         epilogue halves, behind ONE extra quad barrier, so that the pipe works through it during the upper half's epilogue.
-        template <int L> static __host__ __device__ constexpr bool nsplit() { return V >= 1 && L + 1 < N::NL && N::npad(L) >= 128 && (N::npad(L) / chunk_of<N>(L)) % 2 == 0; }
-        template <int L> static __host__ __device__ constexpr bool ksplit_next() { return V >= 2 && nsplit<L>() && (N::kpad(L + 1) / 16) % 2 == 0; }
-
-        // ISSUED: all of layer L was issued by the previous epilogue (PIPELINE); KHALF: its first K half was (ksplit_next<L - 1>)
-        template <int L, bool ISSUED = false, bool KHALF = false>
+        template <int L>
         static __device__ __forceinline__ bool layers(const ll_env<float>& env, const tc_args& a, quad_ctl& ctl, uint32_t tq, uint32_t tt, uint32_t smq_a,
-                                                      const unsigned char* smh, uint32_t mbar, uint32_t mbar2, int q, int wq, int h, int slot, bool run0,
-                                                      bool run1, uint32_t& phase, uint32_t& phase2, ll_lander<float>& p, float cx, float lpad, float lpad_r,
-                                                      int& steps, double& acc, bool& active, unsigned long long member)
+                                                      const unsigned char* smh, uint32_t mbar, int q, int wq, int h, int slot, bool run0, bool run1,
+                                                      uint32_t& phase, ll_lander<float>& p, float cx, float lpad, float lpad_r, int& steps, double& acc,
+                                                      bool& active, unsigned long long member)
         {
-            constexpr int KB = N::kpad(L) / 16;
-            if constexpr (!ISSUED)
+            if constexpr (L > 0)
+            { // the activations this layer reads were written by every thread of the quad: order them before the issue
+                tc05::wait_st();
+                tc05::fence_before_sync();
+                tc05::named_bar_sync(1 + q, QUAD_THREADS);
+                tc05::fence_after_sync();
+            }
+            if (wq == 0)
             {
-                if constexpr (L > 0)
-                { // the activations this layer reads were written by every thread of the quad: order them before the issue
-                    tc05::wait_st();
-                    tc05::fence_before_sync();
-                    tc05::named_bar_sync(1 + q, QUAD_THREADS);
-                    tc05::fence_after_sync();
-                }
-                if (wq == 0)
-                {
-                    if (tc05::elect_one())
-                    {
-                        if constexpr (nsplit<L>())
-                        {
-                            issue_both<N, L, 2, 0>(tq, smq_a, run0, run1, mbar);
-                            issue_both<N, L, 2, 1>(tq, smq_a, run0, run1, mbar2);
-                        }
-                        else issue_both<N, L>(tq, smq_a, run0, run1, mbar, KHALF ? KB / 2 : 0, KB);
-                    }
-                    __syncwarp();
-                }
+                if (tc05::elect_one()) issue_both<N, L>(tq, smq_a, run0, run1, mbar);
+                __syncwarp();
             }
             if (!tc05::mbar_wait(mbar, phase)) return true;
             phase ^= 1u;
             tc05::fence_after_sync();
             if constexpr (L + 1 < N::NL)
             {
-                if constexpr (nsplit<L>())
-                {
-                    constexpr int NC = N::npad(L) / chunk_of<N>(L);
-                    epilogue_hidden<N, L, false, 0, NC / 2>(tt, smh);
-                    if constexpr (ksplit_next<L>())
-                    {
-                        tc05::wait_st();
-                        tc05::fence_before_sync();
-                        tc05::named_bar_sync(1 + q, QUAD_THREADS);
-                        tc05::fence_after_sync();
-                        if (wq == 0)
-                        {
-                            if (tc05::elect_one()) issue_both<N, L + 1>(tq, smq_a, run0, run1, mbar, 0, N::kpad(L + 1) / 32, false);
-                            __syncwarp();
-                        }
-                    }
-                    if (!tc05::mbar_wait(mbar2, phase2)) return true;
-                    phase2 ^= 1u;
-                    tc05::fence_after_sync();
-                    epilogue_hidden<N, L, false, NC / 2, NC>(tt, smh);
-                    return layers<L + 1, false, ksplit_next<L>()>(env, a, ctl, tq, tt, smq_a, smh, mbar, mbar2, q, wq, h, slot, run0, run1, phase, phase2, p, cx, lpad,
-                                                                  lpad_r, steps, acc, active, member);
-                }
-                else
-                {
-                    epilogue_hidden<N, L, pipelined<L>()>(tt, smh, tq, smq_a, run0, run1, mbar, q, wq);
-                    return layers<L + 1, pipelined<L>()>(env, a, ctl, tq, tt, smq_a, smh, mbar, mbar2, q, wq, h, slot, run0, run1, phase, phase2, p, cx, lpad, lpad_r,
-                                                         steps, acc, active, member);
-                }
+                epilogue_hidden<N, L>(tt, smh);
+                return layers<L + 1>(env, a, ctl, tq, tt, smq_a, smh, mbar, q, wq, h, slot, run0, run1, phase, p, cx, lpad, lpad_r, steps, acc, active, member);
             }
             else
             { // ---- output layer: tanh, argmax (first maximum wins), lander update + penalties, next state
@@ -603,11 +523,11 @@ namespace
         }
 
         static __device__ __forceinline__ bool run(const ll_env<float>& env, const tc_args& a, quad_ctl& ctl, uint32_t tq, uint32_t tt, uint32_t smq_a,
-                                                   const unsigned char* smh, uint32_t mbar, uint32_t mbar2, int q, int wq, int h, int slot, bool run0, bool run1,
-                                                   uint32_t& phase, uint32_t& phase2, ll_lander<float>& p, float cx, float lpad, float lpad_r, int& steps,
-                                                   double& acc, bool& active, unsigned long long member)
+                                                   const unsigned char* smh, uint32_t mbar, int q, int wq, int h, int slot, bool run0, bool run1,
+                                                   uint32_t& phase, ll_lander<float>& p, float cx, float lpad, float lpad_r, int& steps, double& acc,
+                                                   bool& active, unsigned long long member)
         {
-            return layers<0>(env, a, ctl, tq, tt, smq_a, smh, mbar, mbar2, q, wq, h, slot, run0, run1, phase, phase2, p, cx, lpad, lpad_r, steps, acc, active, member);
+            return layers<0>(env, a, ctl, tq, tt, smq_a, smh, mbar, q, wq, h, slot, run0, run1, phase, p, cx, lpad, lpad_r, steps, acc, active, member);
         }
     };
 
@@ -619,15 +539,7 @@ namespace
         return v && *v ? atoi(v) : LL_TC05_CUT_DEFAULT;
     }
 
-    // LL_TC05_SPLIT: 0 = a layer's instructions are issued and waited for as one block, 1 / 2 = step_loop's overlap variants
-    int env_split()
-    {
-        const char* v = getenv("LL_TC05_SPLIT");
-        const int s   = v && *v ? atoi(v) : LL_TC05_SPLIT_DEFAULT;
-        return s < 0 ? 0 : (s > 2 ? 2 : s);
-    }
-
-    template <class N, int V> int launch_tc05_v(ll_ctx* ctx, const ll_episode_args& h)
+    template <class N> int launch_tc05_t(ll_ctx* ctx, const ll_episode_args& h)
     {
         const ll_topo& tp = ctx->topo;
         constexpr int NQ  = quads_per_cta<N>();
@@ -660,7 +572,7 @@ namespace
             a.resume.n      = reinterpret_cast<unsigned int*>(base + rec_bytes + 2 * cnt_bytes);
             LL_CUDA(ctx, cudaMemsetAsync(a.resume.n, 0, sizeof(unsigned int), ctx->stream));
         }
-        auto kern         = ll_episode_tc05_kernel<N, V>;
+        auto kern         = ll_episode_tc05_kernel<N>;
         const size_t smem = (size_t)2 * NQ * N::member_bytes + (size_t)NQ * sizeof(quad_ctl);
         LL_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         const unsigned long long ctas_needed = (h.n_members + 2 * NQ - 1) / (2 * NQ);
@@ -677,12 +589,6 @@ namespace
             return n_side ? ll_launch_episode_mmat_resume(ctx, h, a.resume) : ll_launch_episode_mma_resume(ctx, h, a.resume);
         }
         return LL_OK;
-    }
-
-    template <class N> int launch_tc05_t(ll_ctx* ctx, const ll_episode_args& h)
-    {
-        const int v = env_split();
-        return v == 2 ? launch_tc05_v<N, 2>(ctx, h) : (v == 1 ? launch_tc05_v<N, 1>(ctx, h) : launch_tc05_v<N, 0>(ctx, h));
     }
 
     using tnet_32_128_32 = tnet<5, 32, 128, 32, 4>;

@@ -1,6 +1,6 @@
 #!/bin/bash
 # A/B of environment switches on the benchmark workload (c4 shard), device-timed, no CPU legs:
-#   scripts/ab_env.sh <pop_per_gpu> "LL_TC05_SPLIT=0" "LL_TC05_SPLIT=1 LL_TC05_CUT=8" ...   -> gpurun_out/ab_<n>.json + one summary line each
+#   scripts/ab_env.sh <pop_per_gpu> "LL_TC05_CUT=16" "LL_TC05_RESUME=mma LL_TC05_CUT=8" ...   -> gpurun_out/ab_<n>.json + one summary line each
 POP=${1:-32768}; shift
 mkdir -p gpurun_out
 n=0

@@ -11,8 +11,7 @@ import lunar_lander_b200 as ll  # noqa: E402
 cfg_path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "config.txt")
 
 
-KEYS = ("LL_FAST_KERNEL", "LL_MMAT_TILES", "LL_MMA_CHUNKS", "LL_EXACT_CHUNKS", "LL_EXACT_Q", "LL_EXACT_WARP", "LL_TC05_CUT", "LL_TC05_SPLIT", "LL_TC05_RESUME",
-        "LL_TC05_RESUME_WARPS")
+KEYS = ("LL_FAST_KERNEL", "LL_MMAT_TILES", "LL_MMA_CHUNKS", "LL_EXACT_CHUNKS", "LL_EXACT_Q", "LL_EXACT_WARP", "LL_TC05_CUT", "LL_TC05_RESUME")
 
 
 def run(topo, pop, n_layouts, precision, mode, env=None):
@@ -41,7 +40,6 @@ run("16,64,32", 9, 8, 32, 0, {"LL_EXACT_Q": "16"})
 run("32,128,32", 5, 13, 64, 0)
 run("32,128,32", 19, 50, 32, 1, {"LL_FAST_KERNEL": "tc05"})                                   # tile kernel + N-side straggler pass
 run("32,128,32", 19, 50, 32, 1, {"LL_FAST_KERNEL": "tc05", "LL_TC05_RESUME": "mma", "LL_TC05_CUT": "40"})
-run("32,128,32", 19, 50, 32, 1, {"LL_FAST_KERNEL": "tc05", "LL_TC05_RESUME_WARPS": "3", "LL_TC05_SPLIT": "2"})
 run("16,64,32", 45, 33, 32, 1, {"LL_FAST_KERNEL": "tc05", "LL_TC05_CUT": "0"})
 run("32,128,32", 19, 50, 32, 1, {"LL_FAST_KERNEL": "mma"})
 run("32,128,32", 19, 50, 32, 1, {"LL_FAST_KERNEL": "mma", "LL_MMA_CHUNKS": "1"})
