@@ -416,6 +416,9 @@ def measure(ctx, workload, steps, warmup, min_timed_s=1.5, e2e_steps=None, cpu_s
     # with HOST buffers: layouts go in from host memory, fitness / lr / steps come back to host vectors, the host sorts the
     # indices (std::sort in the reference) and hands the order to UpdateWeightsAndBiases.  Copies are inside the timed region.
     # With several ranks the sort is the device top-k + NCCL merge behind ll_select(NULL) (a host sort would need the whole vector).
+    # The sort: what the shipped trainer does at this size (host/nn_engine_trainer.cpp, GpuCfg.select = auto): the reference's host
+    # std::sort up to 65 536 members, the device top-k (ll_select(NULL), elite indices back to the host) above.
+    host_sort = eng.pop_local * world <= 65536
     n_e2e = e2e_steps if e2e_steps is not None else steps
     out = (np.empty(eng.pop_local), np.empty(eng.pop_local), np.empty(eng.pop_local))
     h2d = d2h = 0
@@ -428,9 +431,13 @@ def measure(ctx, workload, steps, warmup, min_timed_s=1.5, e2e_steps=None, cpu_s
         d2h += 3 * 8 * eng.pop_local + 48
         e2e_lander_steps += float(st_steps.sum())
         if world == 1:
-            order = np.argsort(fit, kind="stable").astype(np.uint64)
-            eng.select(order)
-            h2d += 8 * top
+            if host_sort:
+                order = np.argsort(fit, kind="stable").astype(np.uint64)
+                eng.select(order)
+                h2d += 8 * top
+            else:
+                eng.select(None)
+                d2h += 8 * top
             eng.create_population(True)
             eng.update_epochs(1)
         else:
@@ -512,7 +519,9 @@ def measure(ctx, workload, steps, warmup, min_timed_s=1.5, e2e_steps=None, cpu_s
             "e2e": {"value": e2e_lander_steps / e2e_sec if e2e_sec > 0 else 0.0, "unit": "lander-steps/s",
                     "h2d_bytes_per_step": h2d / max(1, n_e2e), "d2h_bytes_per_step": d2h / max(1, n_e2e), "steps": n_e2e,
                     "generations_per_sec": n_e2e / e2e_sec if e2e_sec > 0 else 0.0,
-                    "api": ("ll_evaluate(host layouts -> host fitness/lr/steps) + host argsort + ll_select(sorted) + ll_create_population" if world == 1 else
+                    "api": (("ll_evaluate(host layouts -> host fitness/lr/steps) + host argsort + ll_select(sorted) + ll_create_population" if host_sort else
+                             "ll_evaluate(host layouts -> host fitness/lr/steps) + ll_select(NULL) [device top-k, elite indices to the host; GpuCfg.select = "
+                             "auto above 65 536 members] + ll_create_population") if world == 1 else
                             "per rank: ll_evaluate(host layouts -> host fitness/lr/steps of the shard) + ll_select(NULL) [device top-k, NCCL all-gather, "
                             "device merge, row gather, NCCL all-reduce; elite indices to the host] + ll_create_population")},
         }
