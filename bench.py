@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — lander-steps/sec and generations/sec of the neuro-evolution hot path (BASELINE.json `metric`).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c4|c2|c3|c1|c4_srand] [--scaling weak|strong] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c4|c2|c3|c1|c5|c4_srand] [--scaling weak|strong] [--impl reference]
 
 A "step" is one generation over one batch of synthetic input: evaluate every (member, layout) episode of the
 population (K1), select the elites (K2/K3) and breed the next population (K4).  One JSON line is printed by rank 0.
@@ -15,7 +15,7 @@ Workloads (`--workload`):
   c1  configs[0]: default config.txt (16_16, population 100, 50 layouts), fp64 exact mode
   c4_srand  the c4 topology on an S-rand population (every weight iid N(0,1), redrawn each generation: bimodal 9-step / 5000-step
       episodes, SURVEY.md §8d "stresses divergence"), 16384 members per GPU
-At N = 1 the default line also carries `workloads` = {c1, c2, c3, c4_srand}: short runs of the other BASELINE configs with their own
+At N = 1 the default line also carries `workloads` = {c1, c2, c3, c5, c4_srand}: short runs of the other BASELINE configs with their own
 value / roofline / clocks / cpu_baseline, and every line carries `invariance`: a hash of the fitness vector, elite indices and
 children of one small seeded generation sharded over the N ranks — it must be the same string at N = 1, 2, 4, 8.
 `--scaling strong` fixes the GLOBAL population (c4: 2^20 members) and splits it over the ranks.
@@ -50,6 +50,8 @@ WORKLOADS = {
     "c3": ("16_64_32", 65536, 8, 32, 1, "weak", "configs[2]: 16_64_32, population 65536/GPU x 8 start positions, S-elite, fp32 fast"),
     "c2": ("8_16_8", 4096, 1, 32, 1, "weak", "configs[1]: 8_16_8, population 4096/GPU, single start position, S-elite, fp32 fast"),
     "c1": ("16_16", 100, 50, 64, 0, "weak", "configs[0]: config.txt defaults, 16_16, population 100/GPU x 50 layouts, S-elite, fp64 exact"),
+    "c5": ("8_16_32_16_8", 100, 50, 32, 1, "weak",
+           "configs[4] population: 8_16_32_16_8 deep MLP, config.txt population 100/GPU x 50 layouts, S-elite, fp32 fast (what main_train_f trains)"),
     "c4_srand": ("32_128_32", 16384, 50, 32, 1, "weak",
                  "configs[3] topology on S-rand: 32_128_32, 16384 members/GPU x 50 layouts, every weight iid N(0,1) redrawn each generation, fp32 fast"),
 }
@@ -607,7 +609,7 @@ def run_gpu(args):
     extras = {}
     if world == 1 and not args.no_extras and args.workload == "c4":
         # the other BASELINE configs and the S-rand population, each a short run of its own (>= 1.5 s timed, >= 10 clock samples)
-        for w in ("c1", "c2", "c3", "c4_srand"):
+        for w in ("c1", "c2", "c3", "c5", "c4_srand"):
             r = measure(ctx, w, 3, 3, cpu_seconds=args.extra_cpu_seconds, want_cpu=not args.no_cpu_baseline)
             for k in ("tensor_pipe", "kernel_ms"):
                 r.pop(k, None)
@@ -646,7 +648,7 @@ def main():
     ap.add_argument("--auto-steps", action="store_true", help="raise --steps until the timed region lasts >= 1.5 s (short workloads)")
     ap.add_argument("--e2e-steps", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-extras", action="store_true", help="skip the `workloads` runs (c1, c2, c3, c4_srand) of the default line")
+    ap.add_argument("--no-extras", action="store_true", help="skip the `workloads` runs (c1, c2, c3, c5, c4_srand) of the default line")
     ap.add_argument("--no-invariance", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--extra-cpu-seconds", type=float, default=3.0)

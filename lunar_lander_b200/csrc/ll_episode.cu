@@ -633,7 +633,9 @@ static bool ll_use_warp(const ll_ctx* ctx, int n_layouts)
     const char* force = getenv("LL_FAST_KERNEL");
     if (force && !strcmp(force, "warp")) return true;
     if (force && *force) return false;
-    return n_layouts <= LL_WARP_MAX_LAYOUTS;
+    if (n_layouts <= LL_WARP_MAX_LAYOUTS) return true;
+    // small populations with many layouts (configs[4]: 100 x 50): one warp per episode, 3.2 ms against 6.6 ms on the mma.sync kernel
+    return ll_warp_per_episode(ctx, ctx->pop_local, n_layouts, ctx->d_ep_steps && ctx->d_ep_fit);
 }
 
 int ll_launch_episode(ll_ctx* ctx, const ll_episode_args& a)
@@ -669,7 +671,9 @@ const char* ll_episode_kernel_name(const ll_ctx* ctx, int n_layouts)
         if (ll_exactw_applicable(ctx, probe)) return ctx->precision == 64 ? "ll_episode_exactw_kernel<double> (warp per episode)" : "ll_episode_exactw_kernel<float> (warp per episode)";
     }
     if (ctx->precision == 64) return "ll_episode_kernel<double,exact>";
-    if (ctx->mode == LL_MODE_FAST && ll_use_warp(ctx, n_layouts)) return "ll_episode_warp_kernel (warp per member, FFMA + shuffles)";
+    if (ctx->mode == LL_MODE_FAST && ll_use_warp(ctx, n_layouts))
+        return ll_warp_per_episode(ctx, ctx->pop_local, n_layouts, ctx->d_ep_steps && ctx->d_ep_fit) ? "ll_episode_warp_ep_kernel (warp per episode, FFMA + shuffles)"
+                                                                                                    : "ll_episode_warp_kernel (warp per member, FFMA + shuffles)";
     if (ctx->mode == LL_MODE_FAST && ll_use_tc05(ctx, n_layouts)) return "ll_episode_tc05_kernel (tcgen05 + TMEM; stragglers: mma.sync)";
     if (ctx->mode == LL_MODE_FAST && ll_use_mmat(ctx, n_layouts)) return "ll_episode_mmat_kernel (3 x f16-split mma.sync, slots on N)";
     if (ctx->mode == LL_MODE_FAST && ll_mma_applicable(ctx, n_layouts)) return "ll_episode_mma_kernel (3 x f16-split mma.sync)";

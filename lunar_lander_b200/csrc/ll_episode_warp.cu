@@ -18,6 +18,8 @@
 
 #include "ll_env.cuh"
 
+bool ll_warp_per_episode(const ll_ctx* ctx, unsigned long long n_members, int n_layouts, bool have_episode_arrays);
+
 namespace
 {
     template <int... S> struct wnet
@@ -54,6 +56,7 @@ namespace
         int* ep_steps;
         double* ep_fit;
         unsigned int* queue;
+        unsigned int* part_count; // [n_members] finished episodes of the member (warp-per-episode kernel), zero before the launch
         int p_dev;
         int w_off[LL_MAX_LAYERS], b_off[LL_MAX_LAYERS], out_pad[LL_MAX_LAYERS]; // the HBM row layout (ll_topo)
     };
@@ -144,6 +147,87 @@ namespace
         }
     }
 
+    // ---- small populations with SEVERAL layouts per member (BASELINE.json configs[4]: 8_16_32_16_8, 100 members x 50 start positions,
+    // main_train_f): one warp = one EPISODE.  All members x layouts work items fly at once (longest expected flight first), so a
+    // generation lasts as long as its longest episode's chain of steps instead of a member's episodes one after the other; each
+    // episode's result goes to the per-episode arrays and the member's last episode to finish sums them in layout order.
+    template <class N> __global__ void __launch_bounds__(256) ll_episode_warp_ep_kernel(const __grid_constant__ ll_env<float> env, const __grid_constant__ warp_args a)
+    {
+        static_assert(N::ok(), "topology not supported by the warp-per-episode kernel");
+        const int lane = threadIdx.x & 31;
+        const int L    = a.n_layouts;
+        const unsigned long long n_items = a.n_members * (unsigned long long)L;
+        for (;;)
+        {
+            unsigned long long item = 0;
+            if (lane == 0) item = (unsigned long long)atomicAdd(a.queue, 1u);
+            item = __shfl_sync(0xffffffffu, item, 0);
+            if (item >= n_items) break;
+            const unsigned long long member = item % a.n_members;
+            const int layout                = a.layouts[(int)(item / a.n_members)].next;
+            const float* row                = a.params + member * (size_t)a.p_dev;
+            float w[N::n_w], b[N::NL];
+#pragma unroll
+            for (int l = 0; l < N::NL; ++l)
+            {
+                const bool mine = lane < N::sz(l + 1);
+#pragma unroll
+                for (int k = 0; k < N::sz(l); ++k) w[N::w_at(l) + k] = mine ? __ldg(row + a.w_off[l] + k * a.out_pad[l] + lane) : 0.f;
+                b[l] = mine ? __ldg(row + a.b_off[l] + lane) : 0.f;
+            }
+            const ll_layout<float> lay = a.layouts[layout];
+            ll_lander<float> p{lay.init_x, env.y0, env.vx0, env.vy0, env.max_fuel};
+            const float cx = lay.center_x, lpad = lay.lpad_x1, lpad_r = lay.lpad_right;
+            int steps = 0;
+            double acc = 0.0;
+            bool landed = false, success = false;
+            float dist = 0.f;
+            while (steps < a.max_steps)
+            {
+                float st[5];
+                ll_get_state<float, LL_MODE_FAST>(env, p, cx, st, 1);
+                const float z = forward<N, 0>(w, b, st, 0.f);
+                float best = __shfl_sync(0xffffffffu, z, 0);
+                int action = 0;
+#pragma unroll
+                for (int j = 1; j < N::sz(N::NL); ++j)
+                {
+                    const float zj = __shfl_sync(0xffffffffu, z, j);
+                    if (zj > best) best = zj, action = j; // first maximum wins
+                }
+                const float sp = ll_env_step<float, LL_MODE_FAST>(env, p, action, steps == 0, cx, lpad, lpad_r, &landed, &success, &dist);
+                acc += (double)sp;
+                ++steps;
+                if (landed) break;
+            }
+            if (lane == 0)
+            {
+                const float term = ll_terminal_penalty<float, LL_MODE_FAST>(env, p, steps, landed, success, dist);
+                a.ep_steps[member * (size_t)L + layout] = steps | (landed ? (1 << 28) : 0) | ((landed && !success) ? (1 << 29) : 0) | (success ? (1 << 30) : 0);
+                a.ep_fit[member * (size_t)L + layout]   = (double)term + acc;
+                __threadfence(); // the result is visible device-wide before the arrival is counted
+                if (atomicAdd(a.part_count + member, 1u) == (unsigned int)L - 1u)
+                { // the member's last episode: all layouts in layout order (src/nn_engine_trainer.cpp:518-530)
+                    __threadfence();
+                    a.part_count[member]         = 0u;
+                    const volatile int* g_meta   = a.ep_steps + member * (size_t)L;
+                    const volatile double* g_fit = a.ep_fit + member * (size_t)L;
+                    double f = 0.0, stp = 0.0;
+                    float bonus0 = 0.f, bonus1 = 0.f;
+                    for (int l = 0; l < L; ++l)
+                    {
+                        const int meta = g_meta[l];
+                        f += g_fit[l], stp += (double)(meta & 0x0fffffff);
+                        if (meta & (1 << 30)) (a.layouts[l].dir == 0 ? bonus0 : bonus1) += env.tp_landed_lr_bonus;
+                    }
+                    const double lr   = (double)(bonus1 < bonus0 ? bonus1 : bonus0);
+                    a.fitness[member] = f - lr, a.lr[member] = lr, a.steps[member] = stp;
+                }
+            }
+            __syncwarp();
+        }
+    }
+
     template <class N> int launch_warp_t(ll_ctx* ctx, const ll_episode_args& h)
     {
         const ll_topo& tp = ctx->topo;
@@ -155,6 +239,31 @@ namespace
         for (int l = 0; l < tp.n_layers; ++l) a.w_off[l] = tp.w_off[l], a.b_off[l] = tp.b_off[l], a.out_pad[l] = tp.out_pad[l];
         // spread the members over the SMs first (a generation lasts as long as its longest episode: fewer warps per scheduler =
         // shorter steps), 8 warps per block, persistent warps drawing members from the queue
+        // several layouts per member and room for every episode at once (two waves at most): one warp per EPISODE
+        const unsigned long long items = h.n_members * (unsigned long long)h.n_layouts;
+        if (ll_warp_per_episode(ctx, h.n_members, h.n_layouts, h.ep_steps && h.ep_fit))
+        {
+            const size_t count_bytes = (size_t)h.n_members * sizeof(unsigned int);
+            if (ctx->part_cap < count_bytes)
+            {
+                if (ctx->d_part) cudaFree(ctx->d_part);
+                ctx->d_part = nullptr, ctx->part_cap = 0;
+                LL_CUDA(ctx, cudaMalloc(&ctx->d_part, count_bytes));
+                ctx->part_cap = count_bytes;
+            }
+            a.part_count = static_cast<unsigned int*>(ctx->d_part);
+            LL_CUDA(ctx, cudaMemsetAsync(a.part_count, 0, count_bytes, ctx->stream));
+            int per_sm_e = 0;
+            LL_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_e, ll_episode_warp_ep_kernel<N>, 256, 0));
+            const unsigned long long resident_e = (unsigned long long)ctx->sm_count * std::max(1, per_sm_e);
+            const unsigned int grid_e = (unsigned int)std::max<unsigned long long>(1, std::min(resident_e, (items + 7) / 8));
+            ll_env<float> env_e;
+            ll_make_env<float>(ctx->env_cfg, 1, &env_e);
+            LL_CUDA(ctx, cudaMemsetAsync(h.queue, 0, sizeof(unsigned int), ctx->stream));
+            ll_episode_warp_ep_kernel<N><<<grid_e, 256, 0, ctx->stream>>>(env_e, a);
+            LL_CUDA(ctx, cudaGetLastError());
+            return LL_OK;
+        }
         int per_sm = 0;
         LL_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ll_episode_warp_kernel<N>, 256, 0));
         const unsigned long long resident = (unsigned long long)ctx->sm_count * std::max(1, per_sm);
@@ -181,6 +290,16 @@ namespace
         return true;
     }
 } // namespace
+
+// One warp per EPISODE instead of per member: several layouts per member, the per-episode arrays at hand, and room for every
+// (member, layout) work item within about two waves of resident warps (24 per SM).  LL_WARP_PER_EPISODE = 1 / 0 forces / forbids it.
+bool ll_warp_per_episode(const ll_ctx* ctx, unsigned long long n_members, int n_layouts, bool have_episode_arrays)
+{
+    if (n_layouts <= 1 || !have_episode_arrays) return false;
+    const char* force = getenv("LL_WARP_PER_EPISODE");
+    if (force && *force) return atoi(force) != 0;
+    return n_members * (unsigned long long)n_layouts <= 2ull * (unsigned long long)ctx->sm_count * 24ull;
+}
 
 bool ll_warp_applicable(const ll_ctx* ctx, int n_layouts)
 {

@@ -208,6 +208,7 @@ int ll_launch_episode_exactw(ll_ctx* ctx, const ll_episode_args& a); // ll_episo
 bool ll_exactw_applicable(const ll_ctx* ctx, const ll_episode_args& a);
 int ll_launch_episode_warp(ll_ctx* ctx, const ll_episode_args& a); // ll_episode_warp.cu
 bool ll_warp_applicable(const ll_ctx* ctx, int n_layouts);
+bool ll_warp_per_episode(const ll_ctx* ctx, unsigned long long n_members, int n_layouts, bool have_episode_arrays); // small populations: warp per episode
 #define LL_WARP_MAX_LAYOUTS 1 /* default choice of the warp-per-member kernel: a single layout per member (configs[1]) */
 int ll_launch_feedforward(ll_ctx* ctx, const void* member_row, const void* d_state, unsigned long long* d_action);
 const char* ll_episode_kernel_name(const ll_ctx* ctx, int n_layouts);

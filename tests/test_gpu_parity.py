@@ -760,11 +760,14 @@ def test_fast_tcgen05_kernel_tracks_exact_fp32(ll, po, topo, n_layouts, pop, mon
     assert np.median(rel) <= 1e-5 and np.percentile(rel, 75) <= 1e-3, (np.median(rel), np.percentile(rel, 75), rel.max())
 
 
-@pytest.mark.parametrize("topo,n_layouts,pop", [("8_16_8", 1, 4096), ("16_16", 2, 500), ("8_16_32_16_8", 1, 300), ("16_16", 3, 77)])
+@pytest.mark.parametrize("topo,n_layouts,pop", [("8_16_8", 1, 4096), ("16_16", 2, 500), ("8_16_32_16_8", 1, 300), ("16_16", 3, 77),
+                                                ("8_16_32_16_8", 50, 100), ("16_16", 50, 33), ("8_16_8", 7, 300)])
 def test_fast_warp_per_member_kernel(ll, po, topo, n_layouts, pop, monkeypatch):
-    """ll_episode_warp.cu (one warp = one member, neurons across lanes, weights in registers, shuffles: the configs[1] kernel) against the
-    exact fp32 oracle: unsplit fp32 weights and FFMA, so it tracks the oracle at least as closely as the tensor-core kernels
-    (>= 0.95 of the episodes end at the same step, flags >= 0.99); it is the default for a single layout per member."""
+    """ll_episode_warp.cu (one warp = one member — or, for a small population with several layouts such as configs[4], one warp = one
+    EPISODE — neurons across lanes, weights in registers, shuffles) against the exact fp32 oracle: unsplit fp32 weights and FFMA, so
+    it tracks the oracle at least as closely as the tensor-core kernels (>= 0.95 of the episodes end at the same step, flags >= 0.99).
+    Default for a single layout per member (configs[1]) and where all (member, layout) episodes fit on the GPU at once; the
+    per-member and the per-episode kernel run the same arithmetic per episode: identical per-episode results."""
     members, sizes = util.elite_population(topo, pop, 4, noise=0.02)
     members[pop // 2:] += util.random_population(sizes, pop - pop // 2, 8, scale=0.05)
     spad, lpad, d = util.layouts(50)
@@ -775,7 +778,6 @@ def test_fast_warp_per_member_kernel(ll, po, topo, n_layouts, pop, monkeypatch):
     fit, lr, steps, st = eng.evaluate(spad, lpad, d, 5000)
     assert "_warp_" in eng.info.kernel.decode()
     ep_steps, flags, ep_fit = eng.read_episodes()
-    eng.close()
     assert np.array_equal(steps, ep_steps.sum(axis=1).astype(np.float64)) and st.sum_steps == steps.sum()
     want = po.evaluate(cfg.env_cfg(), sizes, 1, members.astype(np.float32), spad, lpad, d, 5000, 32, threads=8)
     assert np.mean(ep_steps == want["ep_steps"]) >= 0.95
@@ -783,8 +785,22 @@ def test_fast_warp_per_member_kernel(ll, po, topo, n_layouts, pop, monkeypatch):
     rows = np.all(ep_steps == want["ep_steps"], axis=1)
     rel = np.abs(fit[rows] - want["fitness"][rows]) / np.maximum(1.0, np.abs(want["fitness"][rows]))
     assert np.median(rel) <= 1e-5 and np.percentile(rel, 75) <= 1e-3
+    if n_layouts > 1:  # the other work distribution, same arithmetic: per-episode results identical, member sums in layout order both ways
+        per_episode = "_warp_ep_" in eng.info.kernel.decode()
+        monkeypatch.setenv("LL_WARP_PER_EPISODE", "0" if per_episode else "1")
+        other, _ = _engine(ll, sizes, pop, 32, mode=1)
+        other.set_members(0, members)
+        fit2, lr2, steps2, _ = other.evaluate(spad, lpad, d, 5000)
+        assert ("_warp_ep_" in other.info.kernel.decode()) != per_episode
+        s2, f2, e2 = other.read_episodes()
+        other.close()
+        assert np.array_equal(s2, ep_steps) and np.array_equal(f2, flags) and np.array_equal(e2, ep_fit)
+        assert np.array_equal(steps2, steps) and np.array_equal(lr2, lr) and np.allclose(fit2, fit, rtol=1e-12, atol=0)
+        monkeypatch.delenv("LL_WARP_PER_EPISODE")
+    eng.close()
     monkeypatch.delenv("LL_FAST_KERNEL")
     eng, _ = _engine(ll, sizes, pop, 32, mode=1)
     eng.set_layouts(spad, lpad, d)
-    assert ("_warp_" in eng.info.kernel.decode()) == (n_layouts == 1)
+    small = pop * n_layouts <= 2 * 24 * eng.info.sm_count  # every episode resident within two waves: warp per episode by default
+    assert ("_warp_" in eng.info.kernel.decode()) == (n_layouts == 1 or small)
     eng.close()
