@@ -297,3 +297,31 @@ def test_float_population_draws_are_standard_normal(built):
     kids = (p1[10:][~fresh[10:]]).astype(np.float64)
     d = np.abs(kids[:, None, :] - p0[None, :10, :]).mean(axis=2).min(axis=1)
     assert d.max() < 0.15 and d.min() > 0.05                               # children = parent + N(0, 0.1^2): E|d| = 0.08
+
+
+def test_bench_reference_arm_prints_the_contract_line(built):
+    """`bench.py --impl reference` (the driver's reference arm: the reference's own train_generation, oracle/_ref, on the host cores)
+    prints one JSON line with the contract's keys — runs without a GPU."""
+    import json
+    import subprocess
+    import sys
+    p = subprocess.run([sys.executable, os.path.join(util.ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "1", "--ref-step-seconds", "1"],
+                       capture_output=True, text=True, timeout=600, cwd=util.ROOT)
+    assert p.returncode == 0, p.stderr[-2000:]
+    line = json.loads(p.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["metric"] == "lander-steps/sec" and line["higher_is_better"] is True
+    assert line["value"] > 0 and line["unit"] == "lander-steps/s" and line["steps"] == 1 and line["n_gpus"] == 1
+    assert line["cpu_baseline"]["kind"] in ("reference", "port") and line["cpu_baseline"]["cores"] >= 1 and line["cpu_baseline"]["sample"]
+    assert line["e2e"] == {"value": line["value"], "unit": line["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert line["config"]["workload"].startswith("configs[3]")
+
+
+def test_bench_flop_accounting():
+    """The per-step flop figures the bench line's roofline and tensor_pipe keys are built from."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(util.ROOT, "bench.py"))
+    b = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(b)
+    assert b.tc05_flop_per_step([5, 32, 128, 32, 4]) == 52736  # (2 x 32 + 6 x 128 + 24 x 32 + 6 x 8) x 16 x 2
+    sizes = [5, 32, 128, 32, 4]
+    assert sum(2 * sizes[i] * sizes[i + 1] + sizes[i + 1] for i in range(4)) == 17156  # 2 MAC + N, BASELINE.md section 3
