@@ -61,11 +61,45 @@ namespace
         int w_off[LL_MAX_LAYERS], b_off[LL_MAX_LAYERS], out_pad[LL_MAX_LAYERS]; // the HBM row layout (ll_topo)
     };
 
-    // layers L..NL-1 of the forward pass; x = this lane's activation of layer L's input (layer 0: the state, replicated in st)
-    template <class N, int L> __device__ __forceinline__ float forward(const float (&w)[N::n_w], const float (&b)[N::NL], const float (&st)[5], float x)
+    // How a layer's activations reach every lane.  1: through a per-warp shared-memory buffer (one STS, then K / 4 broadcast LDS.128);
+    // 0: one __shfl_sync per input.  A lone warp gets a shuffle result only every ~7.5 cycles (ncu source view), and
+    // a step of 8_16_32_16_8 needs 84 of them against 21 LDS.128 + 6 STS.
+#ifndef LL_WARP_SMEM_EXCHANGE
+#define LL_WARP_SMEM_EXCHANGE 1
+#endif
+
+    // layers L..NL-1 of the forward pass; x = this lane's activation of layer L's input (layer 0: the state, replicated in st);
+    // xb: the warp's exchange buffer, 2 x 32 floats used alternately layer by layer
+    template <class N, int L> __device__ __forceinline__ float forward(const float (&w)[N::n_w], const float (&b)[N::NL], const float (&st)[5], float x, float* xb)
     {
         constexpr int IN = N::sz(L);
         float acc0 = b[L], acc1 = 0.f; // two chains: the dependent FFMA latency is what a step is made of
+#if LL_WARP_SMEM_EXCHANGE
+        float* buf = xb + 32 * (L & 1);
+        if constexpr (L > 0)
+        {
+            buf[threadIdx.x & 31] = x;
+            __syncwarp();
+        }
+#pragma unroll
+        for (int k4 = 0; k4 < (IN + 3) / 4; ++k4)
+        {
+            float4 a4 = make_float4(0.f, 0.f, 0.f, 0.f);
+            if constexpr (L > 0) a4 = reinterpret_cast<const float4*>(buf)[k4];
+            const float av[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+            {
+                const int k = 4 * k4 + j;
+                if (k < IN)
+                {
+                    const float a = L == 0 ? st[k] : av[j];
+                    if (k & 1) acc1 = fmaf(w[N::w_at(L) + k], a, acc1);
+                    else acc0 = fmaf(w[N::w_at(L) + k], a, acc0);
+                }
+            }
+        }
+#else
 #pragma unroll
         for (int k = 0; k < IN; ++k)
         {
@@ -73,14 +107,48 @@ namespace
             if (k & 1) acc1 = fmaf(w[N::w_at(L) + k], a, acc1);
             else acc0 = fmaf(w[N::w_at(L) + k], a, acc0);
         }
+#endif
         const float y = ll_tanh_approx(acc0 + acc1);
-        if constexpr (L + 1 < N::NL) return forward<N, L + 1>(w, b, st, y);
+        if constexpr (L + 1 < N::NL) return forward<N, L + 1>(w, b, st, y, xb);
         else return y;
+    }
+
+    // first maximum of the network's outputs (held by lanes 0 .. n_out - 1), computed by every lane
+    template <class N> __device__ __forceinline__ int argmax_outputs(float z, float* xb)
+    {
+        constexpr int NO = N::sz(N::NL);
+#if LL_WARP_SMEM_EXCHANGE
+        static_assert(NO <= 4, "one LDS.128 holds the outputs");
+        float* buf = xb + 32 * (N::NL & 1);
+        buf[threadIdx.x & 31] = z;
+        __syncwarp();
+        const float4 o4  = reinterpret_cast<const float4*>(buf)[0];
+        __syncwarp(); // every lane has the outputs before the next step's first exchange may reuse this buffer
+        const float o[4] = {o4.x, o4.y, o4.z, o4.w};
+        float best = o[0];
+        int action = 0;
+#pragma unroll
+        for (int j = 1; j < NO; ++j)
+            if (o[j] > best) best = o[j], action = j;
+        return action;
+#else
+        float best = __shfl_sync(0xffffffffu, z, 0);
+        int action = 0;
+#pragma unroll
+        for (int j = 1; j < NO; ++j)
+        {
+            const float zj = __shfl_sync(0xffffffffu, z, j);
+            if (zj > best) best = zj, action = j;
+        }
+        return action;
+#endif
     }
 
     template <class N> __global__ void __launch_bounds__(256) ll_episode_warp_kernel(const __grid_constant__ ll_env<float> env, const __grid_constant__ warp_args a)
     {
         static_assert(N::ok(), "topology not supported by the warp-per-member episode kernel");
+        __shared__ __align__(16) float s_xb[8][64];
+        float* xb      = s_xb[threadIdx.x >> 5];
         const int lane = threadIdx.x & 31;
         for (;;)
         {
@@ -114,16 +182,8 @@ namespace
                 {
                     float st[5];
                     ll_get_state<float, LL_MODE_FAST>(env, p, cx, st, 1);
-                    const float z = forward<N, 0>(w, b, st, 0.f);
-                    // argmax over the outputs (first maximum wins), every lane computes it
-                    float best = __shfl_sync(0xffffffffu, z, 0);
-                    int action = 0;
-#pragma unroll
-                    for (int j = 1; j < N::sz(N::NL); ++j)
-                    {
-                        const float zj = __shfl_sync(0xffffffffu, z, j);
-                        if (zj > best) best = zj, action = j;
-                    }
+                    const float z    = forward<N, 0>(w, b, st, 0.f, xb);
+                    const int action = argmax_outputs<N>(z, xb); // first maximum wins, every lane computes it
                     const float sp = ll_env_step<float, LL_MODE_FAST>(env, p, action, steps == 0, cx, lpad, lpad_r, &landed, &success, &dist);
                     acc += (double)sp;
                     ++steps;
@@ -154,6 +214,8 @@ namespace
     template <class N> __global__ void __launch_bounds__(256) ll_episode_warp_ep_kernel(const __grid_constant__ ll_env<float> env, const __grid_constant__ warp_args a)
     {
         static_assert(N::ok(), "topology not supported by the warp-per-episode kernel");
+        __shared__ __align__(16) float s_xb[8][64];
+        float* xb      = s_xb[threadIdx.x >> 5];
         const int lane = threadIdx.x & 31;
         const int L    = a.n_layouts;
         const unsigned long long n_items = a.n_members * (unsigned long long)L;
@@ -186,15 +248,8 @@ namespace
             {
                 float st[5];
                 ll_get_state<float, LL_MODE_FAST>(env, p, cx, st, 1);
-                const float z = forward<N, 0>(w, b, st, 0.f);
-                float best = __shfl_sync(0xffffffffu, z, 0);
-                int action = 0;
-#pragma unroll
-                for (int j = 1; j < N::sz(N::NL); ++j)
-                {
-                    const float zj = __shfl_sync(0xffffffffu, z, j);
-                    if (zj > best) best = zj, action = j; // first maximum wins
-                }
+                const float z    = forward<N, 0>(w, b, st, 0.f, xb);
+                const int action = argmax_outputs<N>(z, xb); // first maximum wins
                 const float sp = ll_env_step<float, LL_MODE_FAST>(env, p, action, steps == 0, cx, lpad, lpad_r, &landed, &success, &dist);
                 acc += (double)sp;
                 ++steps;
