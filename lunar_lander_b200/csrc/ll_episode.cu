@@ -672,8 +672,8 @@ const char* ll_episode_kernel_name(const ll_ctx* ctx, int n_layouts)
     }
     if (ctx->precision == 64) return "ll_episode_kernel<double,exact>";
     if (ctx->mode == LL_MODE_FAST && ll_use_warp(ctx, n_layouts))
-        return ll_warp_per_episode(ctx, ctx->pop_local, n_layouts, ctx->d_ep_steps && ctx->d_ep_fit) ? "ll_episode_warp_ep_kernel (warp per episode, FFMA + smem exchange)"
-                                                                                                    : "ll_episode_warp_kernel (warp per member, FFMA + smem exchange)";
+        return ll_warp_per_episode(ctx, ctx->pop_local, n_layouts, ctx->d_ep_steps && ctx->d_ep_fit) ? "ll_episode_warp_ep_kernel (warp per episode, FFMA + smem)"
+                                                                                                    : "ll_episode_warp_kernel (warp per member, FFMA + smem)";
     if (ctx->mode == LL_MODE_FAST && ll_use_tc05(ctx, n_layouts)) return "ll_episode_tc05_kernel (tcgen05 + TMEM; stragglers: mma.sync)";
     if (ctx->mode == LL_MODE_FAST && ll_use_mmat(ctx, n_layouts)) return "ll_episode_mmat_kernel (3 x f16-split mma.sync, slots on N)";
     if (ctx->mode == LL_MODE_FAST && ll_mma_applicable(ctx, n_layouts)) return "ll_episode_mma_kernel (3 x f16-split mma.sync)";
