@@ -167,7 +167,10 @@ int ll_synchronize(ll_ctx* ctx);
 /* ---- GA -----------------------------------------------------------------------------------------------
  * replaces  SetPopulationStrategy(MIXED_WITH_RANDOM_INJECTION, ratio)   src/nn_engine_trainer.cpp:93 */
 int ll_set_population_strategy(ll_ctx* ctx, int strategy, double random_injection_ratio);
-/* replaces  CreatePopulation(elitism)   src/nn_engine_trainer.cpp:94 (initial) and :405 (per generation) */
+/* replaces  CreatePopulation(elitism)   src/nn_engine_trainer.cpp:94 (initial) and :405 (per generation).
+ * Every draw is a function of (seed, generation, GLOBAL member, position): the children do not depend on the GPU count.  In
+ * LL_MODE_EXACT the normals are reproducible bit for bit on the host (csrc/ll_philox.h, what the oracle runs); in LL_MODE_FAST
+ * (fp32) they come from the GPU's special-function unit: deterministic on the device, judged statistically. */
 int ll_create_population(ll_ctx* ctx, int elitism);
 /* standard deviations of the initial / injected individuals and of the mutation noise (values <= 0 keep the current
  * ones; ma-libs' own constants are not recoverable, SURVEY.md App. C — defaults 1.0 and 0.1) */
